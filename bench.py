@@ -1,0 +1,332 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the geometric-conditioning hot path (BASELINE.json `metric`).
+
+One "step" = one pass of the hot path over one trajectory batch: config B, 3 source RGB-D views ->
+25 target frames at 576x1024, PAIR mode (75 pair warps): forward warp (colour f32 + hole mask + winner
+index) + reprojection-consistency masks per pair.  metric = target-view Mpix/s = T*H*W / time.
+
+  python bench.py [--gpus N --steps K --warmup W]            our CUDA path (torchrun for N > 1)
+  python bench.py --impl reference [...]                     the CPU restatement of the reference on host cores
+
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every field.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from syn3r_b200 import synth  # noqa: E402
+
+METRIC = "target_view_mpix_per_s_warped_masked"
+UNIT = "Mpix/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="B_svd", choices=list(synth.CONFIGS))
+    ap.add_argument("--pairs", default="all", choices=["all", "reference_policy"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-sample-seconds", type=float, default=12.0)
+    return ap.parse_args()
+
+
+def workload_desc(args, S, T, H, W, P):
+    return {"workload": f"{args.config}: {S} src RGB-D f32 -> {T} target poses at {H}x{W}, PAIR mode ({P} pair warps), "
+                        "forward soft-z splat (rgb f32 + hole mask + winner idx) + reprojection consistency "
+                        "(mask_reproj u8 + soft_mask f32) per pair",
+            "S": S, "T": T, "H": H, "W": W, "pairs": P, "pair_policy": args.pairs,
+            "l2_policy": "256 MiB buffer written between timed iterations (L2 flush); outputs 973 MB >> 126 MB L2"}
+
+
+def pair_lists(args, S, T):
+    return synth.all_pairs(S, T) if args.pairs == "all" else synth.reference_policy_pairs(T, S)
+
+
+# -------------------------------------------------------------------------------------------------
+# CPU legs (oracle port = C restatement of the reference; /root/reference cannot travel to the GPU box)
+# -------------------------------------------------------------------------------------------------
+
+def _cpu_one_pair(job):
+    """forward_warp (+ winner) and inverse_warp-style consistency of ONE pair through the oracle port."""
+    import torch
+    from oracle import cpu_oracle as orc
+    tr, s, t = job
+    t_ = torch.from_numpy
+    with np.errstate(all="ignore"):
+        orc.forward_warp_ext([tr.rgb[s]], [None], [tr.depth[s]], [tr.pose_src[s]], tr.pose_tgt[t], [tr.K], None)
+        orc.inverse_warp(t_(np.ascontiguousarray(np.moveaxis(tr.rgb[s], -1, 0))), t_(tr.depth[s][None]),
+                         t_(tr.depth_tgt[t][None]), t_(tr.pose_src[s]), t_(tr.pose_tgt[t]),
+                         t_(tr.K.astype(np.float32)))
+    return 1
+
+
+_G = {}
+
+
+def _pool_job(i):
+    tr, ps, pt = _G["tr"], _G["ps"], _G["pt"]
+    return _cpu_one_pair((tr, int(ps[i % len(ps)]), int(pt[i % len(pt)])))
+
+
+def cpu_baseline_sample(tr, ps, pt, seconds):
+    """Scalar oracle port on ONE host core over a bounded sample of the same pairs."""
+    from oracle import cpu_oracle as orc
+    orc.lib()
+    S, T, H, W = tr.shape
+    _cpu_one_pair((tr, int(ps[0]), int(pt[0])))           # warm (page in, build)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        _cpu_one_pair((tr, int(ps[n % len(ps)]), int(pt[n % len(pt)])))
+        n += 1
+        el = time.perf_counter() - t0
+        if el >= seconds or n >= len(ps):
+            break
+    pairs_per_view = len(ps) / T
+    val = (n / pairs_per_view) * H * W / el / 1e6
+    return {"value": val, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": f"{n} of {len(ps)} pair warps (forward+winner and inverse/consistency) at {H}x{W} in {el:.1f} s, "
+                      f"oracle/syn3r_oracle.c single thread; target-view rate = pair rate / {pairs_per_view:g}"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU algorithm (oracle port) on all host cores, frames farmed over a
+    process pool (frames are independent, SURVEY §8d 'fair multi-core')."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    from oracle import cpu_oracle as orc
+    orc.build()
+    S, T, H, W = synth.CONFIGS[args.config]
+    tr = synth.make_trajectory(S, T, H, W, seed=0)
+    ps, pt = pair_lists(args, S, T)
+    cores = os.cpu_count() or 1
+    workers = max(1, min(cores, 64))
+    per_step = min(len(ps), max(workers, 8))                # bounded sample of the 75-pair step
+    _G.update(tr=tr, ps=ps, pt=pt)
+    ctx = mp.get_context("fork")
+    with ctx.Pool(workers) as pool:
+        for _ in range(max(args.warmup, 1)):
+            pool.map(_pool_job, range(workers), chunksize=1)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            pool.map(_pool_job, range(per_step), chunksize=1)
+        el = time.perf_counter() - t0
+    pairs_per_view = len(ps) / T
+    val = (args.steps * per_step / pairs_per_view) * H * W / el / 1e6
+    sample = (f"{per_step} of {len(ps)} pair warps per step at {H}x{W}, {workers} worker processes "
+              f"(os.cpu_count()={cores}), oracle/syn3r_oracle.c")
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": el / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64 forward / f32 backward",
+            "data": "synthetic", "config": workload_desc(args, S, T, H, W, len(ps)),
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": workers, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# -------------------------------------------------------------------------------------------------
+# GPU arm
+# -------------------------------------------------------------------------------------------------
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled every 200 ms DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def __enter__(self):
+        try:
+            f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
+            self.path = f.name
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=f,
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+        return self
+
+    def __exit__(self, *a):
+        if self.proc is not None:
+            time.sleep(0.25)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        try:
+            rows = [r.split(",") for r in open(self.path).read().strip().splitlines() if r.strip()]
+            sm = [float(r[0]) for r in rows]
+            out["samples"] = len(sm)
+            if sm:
+                out["sm_mhz"] = statistics.median(sm)
+                out["sm_max_mhz"] = float(rows[0][1])
+                out["power_w_max"] = max(float(r[2]) for r in rows)
+                names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+                out["reasons"] = [n for i, n in enumerate(names) if any("Active" == r[3 + i].strip() for r in rows)]
+            os.unlink(self.path)
+        except Exception as e:  # noqa: BLE001
+            out["error"] = str(e)
+        return out
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from syn3r_b200 import _native as nat, trajectory, warp as w
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py (impl=ours) needs a GPU; there is no CPU fallback"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    nat.lib()
+
+    S, T, H, W = synth.CONFIGS[args.config]
+    tr = synth.make_trajectory(S, T, H, W, seed=rank)        # weak scaling: one trajectory per rank
+    ps, pt = pair_lists(args, S, T)
+    tw = trajectory.from_synth(tr, pairs=(ps, pt), want_f32=True, want_u8=False, want_winner=True,
+                               pinned_host=not args.no_e2e)
+    rgbd_h = torch.from_numpy(w.pack_rgbd(tr.rgb, tr.depth))
+    tgtd_h = torch.from_numpy(tr.depth_tgt)
+    if not args.no_e2e:
+        tw.pinned["rgbd"].copy_(rgbd_h)
+        tw.pinned["tgt_depth"].copy_(tgtd_h)
+        rgbd_h, tgtd_h = tw.pinned["rgbd"], tw.pinned["tgt_depth"]
+    tw.upload(rgbd_h, tgtd_h)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def timed(fn, steps, between=None):
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        torch.cuda.synchronize()
+        barrier()
+        for e0, e1 in evs:
+            if between is not None:
+                between()
+            e0.record()
+            fn()
+            e1.record()
+        torch.cuda.synchronize()
+        barrier()
+        return [e0.elapsed_time(e1) for e0, e1 in evs]
+
+    for _ in range(max(args.warmup, 3)):
+        tw.run()
+    torch.cuda.synchronize()
+    assert int(tw.out_fwd["status"].max().item()) == 0, "colour range check failed"
+
+    # ---- device-resident throughput (`value`) ------------------------------------------------------
+    with ClockSampler(local) as cs:
+        ms = timed(tw.run, args.steps, between=flush.zero_)
+    clocks = cs.summary()
+    total_ms = sum(ms)
+    if world > 1:
+        tt = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        total_ms = float(tt.item())
+    mpix_step = T * H * W / 1e6
+    value = world * args.steps * mpix_step / (total_ms / 1e3)
+
+    # ---- per-kernel durations (CUDA events on the launching stream, phases launched one at a time) ---
+    def phase(bits):
+        return lambda: w.forward_warp_batched(tw.rgbd, tw.Kinv_src, tw.pair_par, tw.pair_src, want_f32=True,
+                                              want_u8=False, want_winner=True, out=tw.out_fwd, phases=bits)
+
+    def inv():
+        return w.inverse_warp_batched(None, None, tw.tgt_depth, tw.K_host, tw.pair_P, tw.pair_src, tw.pair_tgt,
+                                      rgbd=tw.rgbd, bandwidth=tw.bandwidth, want=("mask_reproj", "soft_mask_reproj"),
+                                      out=tw.out_inv)
+
+    kern = {}
+    n_k = max(3, min(args.steps, 10))
+    for name, fn in (("fwd_init+zmax", phase(nat.FWD_PHASE_ZMAX)), ("fwd_splat", phase(nat.FWD_PHASE_SPLAT)),
+                     ("fwd_resolve", phase(nat.FWD_PHASE_RESOLVE)), ("inverse_consistency", inv)):
+        kern[name] = statistics.mean(timed(fn, n_k, between=flush.zero_))
+    ksum = sum(kern.values())
+    dominant = max(kern, key=kern.get)
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    b_alg = tw.algorithmic_bytes()
+    achieved = b_alg / (ksum / 1e3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback",
+                "algorithmic_bytes_per_step": b_alg,
+                "scope": "all kernels of one step (init+zmax, splat, resolve, inverse); SURVEY 8d B_alg / their summed "
+                         "event time",
+                "dominant_kernel": dominant, "kernel_ms": kern,
+                "kernel_share": {k: v / ksum for k, v in kern.items()}}
+
+    # ---- end to end through the plan with HOST buffers ------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        def step_e2e():
+            tw.upload(rgbd_h, tgtd_h)
+            tw.run()
+            tw.download()
+        for _ in range(2):
+            step_e2e()
+        ms_e = timed(step_e2e, args.steps)
+        tot = sum(ms_e)
+        if world > 1:
+            tt = torch.tensor([tot], device=dev, dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            tot = float(tt.item())
+        e2e = {"value": world * args.steps * mpix_step / (tot / 1e3), "unit": UNIT,
+               "h2d_bytes_per_step": tw.h2d_bytes(), "d2h_bytes_per_step": tw.d2h_bytes(),
+               "ms_per_step": tot / args.steps}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline_sample(tr, ps, pt, args.cpu_sample_seconds)
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64 projection / f32 accumulate", "data": "synthetic",
+                "config": workload_desc(args, S, T, H, W, len(ps)), "clocks": clocks, "e2e": e2e,
+                "gpu_launches": args.steps * tw.launches_per_run(), "roofline": roofline, "cpu_baseline": cpu,
+                "pair_mpix_per_s": world * args.steps * len(ps) * H * W / 1e6 / (total_ms / 1e3)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

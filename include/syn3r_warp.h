@@ -1,0 +1,158 @@
+/* syn3r_warp.h — C ABI of libsyn3r_warp.so (hand-written sm_100a CUDA, no torch types).
+ *
+ * Drop-in boundary for ONE hot path of DecaYale/SYN3R @ 402f4e9: the geometric conditioning step
+ * (solver_utils/forward_warp.py + solver_utils/consistency.py).  The reference has no FFI for this
+ * path — its module-level Python functions ARE the interface — so each entry point
+ * below names the reference function(s) it replaces (paths relative to the reference root); the
+ * Python mirror of those functions (package syn3r_b200.solver_utils) binds them with ctypes, and
+ * INTEGRATION.md shows the stub a maintainer would drop into the reference tree.
+ *
+ * Conventions
+ *   - Every pointer is a DEVICE pointer unless the comment says "host".  Arrays are dense, C order.
+ *   - `stream` is a cudaStream_t passed as void*.  All work is enqueued on it; no entry point
+ *     allocates, synchronises, or keeps mutable global state (apart from a thread-local error
+ *     string).  Outputs and the workspace are caller-owned.
+ *   - Return value: 0 = SYN3R_OK, otherwise one of the SYN3R_E* codes; syn3r_last_error() gives
+ *     a human-readable reason.  No C++ exception crosses the boundary.
+ *   - Poses are world-to-camera 4x4 [R t; 0 1] (forward_warp.py:151-152, consistency.py:30-31);
+ *     K is a pixel-unit pinhole 3x3.  Small matrices (inverses, pose products) are prepared by
+ *     the caller with the SAME library calls the reference makes (np.linalg.inv / np.matmul in
+ *     the caller's dtype, torch.inverse / @ in fp32) so their rounding is the reference's.
+ *   - A "pair" is one (source view, target pose) warp = one call of the reference's per-frame
+ *     function.  A "slot" is one output frame: PAIR mode -> slot == pair (reference semantics);
+ *     FUSED mode -> several pairs (sources) accumulate into one slot (extension).
+ */
+#ifndef SYN3R_WARP_H
+#define SYN3R_WARP_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SYN3R_ABI_VERSION 3
+
+enum {
+    SYN3R_OK = 0,
+    SYN3R_EARG = 1,       /* bad argument (null pointer, non-positive size, bad flag combination) */
+    SYN3R_EWORKSPACE = 2, /* workspace too small or misaligned (needs 256-byte alignment)        */
+    SYN3R_ECUDA = 3,      /* a CUDA runtime call / kernel launch failed                           */
+    SYN3R_EDEVICE = 4     /* current device is not compute capability 10.x                        */
+};
+
+/* flags of the forward path */
+enum {
+    SYN3R_FWD_GATE_0P6 = 1 << 0, /* mask &= (sum of weights <= 0.6): model/SVD_1pass.py:853-855         */
+    SYN3R_FWD_WINNER = 1 << 1,   /* emit the deterministic winner index (extension, 64-bit atomicMin)   */
+    SYN3R_FWD_IS_IMAGE = 1 << 2, /* range check + clip[0,255] + round-half-even (forward_warp.py:119-128)*/
+    SYN3R_FWD_FAST_WEIGHT = 1 << 3 /* soft-depth weight via the short fp64 polynomial path (rel. err
+                                      < 1e-9: masks unchanged, colours far inside 1e-5); without it
+                                      the weight uses IEEE log/exp/div like the reference            */
+    /* measurement aid: run only the named phase(s) of syn3r_forward_warp_batched so a caller can
+       bracket each kernel with its own CUDA events; no bit set = all three phases */
+    , SYN3R_FWD_PHASE_ZMAX = 1 << 8    /* workspace init + per-pair max z' reduction */
+    , SYN3R_FWD_PHASE_SPLAT = 1 << 9   /* project + splat                             */
+    , SYN3R_FWD_PHASE_RESOLVE = 1 << 10 /* normalise + masks + winner                  */
+};
+
+int syn3r_version(void);
+const char *syn3r_last_error(void);
+
+/* Number of SMs / max opt-in shared memory of the current device (host query, cached). */
+int syn3r_device_info(int *sm_count, int *smem_optin_bytes, int *cc_major, int *cc_minor);
+
+/* ---------------------------------------------------------------------------------------------
+ * Forward path: compute_transformed_points (forward_warp.py:7-37) + forward_warp (:141-182) +
+ * bilinear_splatting (:41-129), batched over pairs.
+ *
+ *   rgbd      [S,H,W,4] f32   source colour (0..255 scale) + z-depth, one float4 per pixel
+ *   depth64   [S,H,W]   f64   nullable; when given it replaces rgbd[...,3] (callers with f64 depth)
+ *   src_mask  [S,H,W]   u8    nullable; mask1 of forward_warp.py:56 (0 = unknown pixel)
+ *   Kinv_src  [S,9]     f64   np.linalg.inv(intrinsic1) (:25)
+ *   pair_par  [P,24]    f64   per pair: M = (T2 @ inv(T1))[:3,:] row-major (12), intrinsic2 (9), 3 pad
+ *   pair_src  [P]       i32   source index of each pair
+ *   pair_slot [P]       i32   nullable -> slot = pair index (PAIR mode)
+ *   out_rgb_f32 [n_slots,H,W,3] f32  nullable: normalised colour before rounding (:116)
+ *   out_rgb_u8  [n_slots,H,W,3] u8   nullable: clipped + rounded (:127-128), needs IS_IMAGE
+ *   out_mask    [n_slots,H,W]   u8   mask2 (:112), 0/1
+ *   out_winner  [n_slots,H,W]   i32  nullable, needs WINNER: src*H*W + y*W + x of the contributing
+ *                                     source pixel with the smallest (float)z', ties -> smallest
+ *                                     index; -1 = hole
+ *   out_flow    [P,H,W,2]  f64  nullable: flow12 (:177)
+ *   out_status  [n_slots]  i32  nullable: bit0 = colour-range assert of :121-125 failed
+ *   workspace   >= syn3r_fwd_workspace_bytes(...) bytes, 256-byte aligned
+ * ------------------------------------------------------------------------------------------- */
+size_t syn3r_fwd_workspace_bytes(int H, int W, int n_pairs, int n_slots, int flags);
+
+int syn3r_forward_warp_batched(const float *rgbd, const double *depth64, const uint8_t *src_mask,
+                               const double *Kinv_src, const double *pair_par, const int32_t *pair_src,
+                               const int32_t *pair_slot, int S, int P, int n_slots, int H, int W, int flags,
+                               float *out_rgb_f32, uint8_t *out_rgb_u8, uint8_t *out_mask, int32_t *out_winner,
+                               double *out_flow, int32_t *out_status, void *workspace, size_t workspace_bytes,
+                               void *stream);
+
+/* compute_transformed_points (forward_warp.py:7-37) on its own: q = K2 (M [d K1inv p; 1])[:3] and
+ * X = d K1inv p, both [H,W,3] f64.  depth [H,W] f64, par = one pair_par record, Kinv [9]. */
+int syn3r_compute_transformed_points(const double *depth, const double *Kinv, const double *par, int H, int W,
+                                     double *out_q, double *out_X, void *stream);
+
+/* bilinear_splatting (forward_warp.py:41-129) on its own, from caller-supplied flow and depth:
+ *   frame [H,W,C] f32 (C <= 3), mask1 / flow_mask [H,W] u8 nullable, z [H,W] f64 (the `depth1`
+ *   argument, i.e. z'), flow [H,W,2] f64.  out [H,W,C] f32 (nullable), out_u8 [H,W,C] (nullable,
+ *   IS_IMAGE), out_mask [H,W] u8, out_status [1] i32 nullable.  Workspace as for P = n_slots = 1. */
+int syn3r_bilinear_splat(const float *frame, const uint8_t *mask1, const double *z, const double *flow,
+                         const uint8_t *flow_mask, int H, int W, int C, int flags, float *out, uint8_t *out_u8,
+                         uint8_t *out_mask, int32_t *out_status, void *workspace, size_t workspace_bytes,
+                         void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Backward path: inverse_warp (forward_warp.py:187-279) incl. its consistency_check_with_depth
+ * call (:259 -> consistency.py:44-91), batched over pairs.  All fp32.
+ *
+ *   src_img   [S,3,H,W] f32 (nullable when no colour output is requested)
+ *   src_depth [S,H,W] f32 with src_depth_stride = 1, or the depth lane of the forward path's
+ *             [S,H,W,4] RGB-D buffer (pointer = rgbd + 3, src_depth_stride = 4)
+ *   src_bg    [S,H,W] u8 nullable (bg_mask, :232)
+ *   tgt_depth [T,H,W] f32  (depth_pseudo)
+ *   K, Kinv   [9] f32 HOST (Kinv = torch.inverse(K), consistency.py:21); passed by value to the kernels
+ *   pair_P    [P,2,16] f32 per pair: pose1 @ inverse(pose2) (:217) then pose2 @ inverse(pose1)
+ *   pair_src / pair_tgt [P] i32
+ *   outputs, each nullable, one plane set per pair: warped_img [P,3,H,W], warped_depth [P,H,W],
+ *   warped_masked_img [P,3,H,W], soft_mask_reproj [P,H,W], reproj_err [P,H,W] f32; mask_warp,
+ *   mask_depth, mask, mask_inv, mask_depth_strict, warped_bg, mask_reproj [P,H,W] u8 (0/1).
+ *   The depth-normalisation masks need a per-pair min/max pre-pass (:236-240); it only runs when
+ *   one of mask_depth / mask / mask_inv / mask_depth_strict / warped_masked_img is requested.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct syn3r_inv_outputs {
+    float *warped_img, *warped_depth, *warped_masked_img, *soft_mask_reproj, *reproj_err;
+    uint8_t *mask_warp, *mask_depth, *mask, *mask_inv, *mask_depth_strict, *warped_bg, *mask_reproj;
+} syn3r_inv_outputs;
+
+size_t syn3r_inv_workspace_bytes(int n_pairs);
+
+int syn3r_inverse_warp_batched(const float *src_img, const float *src_depth, int src_depth_stride,
+                               const uint8_t *src_bg,
+                               const float *tgt_depth, const float *K, const float *Kinv, const float *pair_P,
+                               const int32_t *pair_src, const int32_t *pair_tgt, int P, int H, int W,
+                               float bandwidth, float thr_depth, float thr_depth_strict,
+                               const syn3r_inv_outputs *out /* host struct of device pointers */,
+                               void *workspace, size_t workspace_bytes, void *stream);
+
+/* consistency_check_with_depth (consistency.py:44-91), batched: frame 1 = depth1[pair_1[p]],
+ * frame 2 = depth2[pair_2[p]]; K1, K1inv, K2 [9] f32 HOST, shared; pair_T [P,2,16] f32 = pose2 @ inv(pose1)
+ * then pose1 @ inv(pose2) (consistency.py:39).  err [P,H,W] f32 (pixels). */
+int syn3r_consistency_batched(const float *depth1, const float *depth2, const float *K1, const float *K1inv,
+                              const float *K2, const float *pair_T, const int32_t *pair_1, const int32_t *pair_2,
+                              int P, int H, int W, float *err, void *stream);
+
+/* get_points_from_depth (consistency.py:6-23): pts [H,W,3] = (Kinv [x,y,1]) * depth.  Kinv [9] HOST. */
+int syn3r_points_from_depth(const float *depth, const float *Kinv, int H, int W, float *pts, void *stream);
+/* transform_points (consistency.py:25-42): T [16] HOST = pose2 @ inverse(pose1); out = (T [p;1])[:3] / w. */
+int syn3r_transform_points(const float *pts, const float *T, int H, int W, float *out, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SYN3R_WARP_H */

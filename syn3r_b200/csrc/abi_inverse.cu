@@ -1,0 +1,118 @@
+// abi_inverse.cu — extern "C" launchers of the backward / consistency path (include/syn3r_warp.h).
+#include <string.h>
+
+#include "inverse_kernels.cuh"
+
+using namespace syn3r;
+
+namespace {
+
+dim3 stride_grid2(size_t n, int per_block, int ny) {
+    size_t need = (n + per_block - 1) / per_block;
+    size_t cap = (size_t)sm_count() * 8;
+    size_t gx = need;
+    if ((size_t)ny * need > cap) {
+        gx = (cap + ny - 1) / ny;
+        if (gx < 1) gx = 1;
+        if (gx > need) gx = need;
+    }
+    return dim3((unsigned)gx, (unsigned)ny, 1);
+}
+
+CamF32 make_cam(const float *K1, const float *K1inv, const float *K2, int H, int W) {
+    CamF32 c;
+    memcpy(c.K1, K1, sizeof(c.K1));
+    memcpy(c.K1inv, K1inv, sizeof(c.K1inv));
+    memcpy(c.K2, K2, sizeof(c.K2));
+    c.half_wm1 = (float)((double)(W - 1) / 2.0);
+    c.half_hm1 = (float)((double)(H - 1) / 2.0);
+    c.half_w = (float)W / 2.0f;
+    c.half_h = (float)H / 2.0f;
+    return c;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t syn3r_inv_workspace_bytes(int n_pairs) {
+    if (n_pairs <= 0) return 0;
+    return ((size_t)n_pairs * 16 + 255) / 256 * 256;
+}
+
+int syn3r_inverse_warp_batched(const float *src_img, const float *src_depth, int src_depth_stride,
+                               const uint8_t *src_bg,
+                               const float *tgt_depth, const float *K, const float *Kinv, const float *pair_P,
+                               const int32_t *pair_src, const int32_t *pair_tgt, int P, int H, int W,
+                               float bandwidth, float thr_depth, float thr_depth_strict,
+                               const syn3r_inv_outputs *out, void *workspace, size_t workspace_bytes, void *stream) {
+    SYN3R_REQUIRE(src_depth && tgt_depth && K && Kinv && pair_P && pair_src && pair_tgt && out,
+                  "null required pointer");
+    SYN3R_REQUIRE(src_img || !(out->warped_img || out->warped_masked_img), "colour outputs need src_img");
+    SYN3R_REQUIRE(src_depth_stride == 1 || src_depth_stride == 4, "src_depth_stride must be 1 or 4");
+    SYN3R_REQUIRE(P > 0 && H > 0 && W > 0, "non-positive size");
+    SYN3R_REQUIRE((size_t)H * W < 0x7fffffffull, "H*W must fit int32");
+    int rc = check_device();
+    if (rc != SYN3R_OK) return rc;
+    const bool need_minmax = out->mask_depth || out->mask || out->mask_inv || out->mask_depth_strict ||
+                             out->warped_masked_img;
+    cudaStream_t st = (cudaStream_t)stream;
+    uint32_t *ws = nullptr;
+    if (need_minmax) {
+        if (!workspace || workspace_bytes < syn3r_inv_workspace_bytes(P) || ((uintptr_t)workspace & 255)) {
+            set_error("inverse workspace: need %zu bytes, 256-byte aligned (got %zu)", syn3r_inv_workspace_bytes(P),
+                      workspace_bytes);
+            return SYN3R_EWORKSPACE;
+        }
+        ws = (uint32_t *)workspace;
+    }
+    CamF32 cam = make_cam(K, Kinv, K, H, W);
+    InvPairs pr{pair_P, pair_src, pair_tgt};
+    const size_t hw = (size_t)H * W;
+    dim3 g = stride_grid2(hw, 256, P);
+    if (need_minmax) {
+        k_inv_init_minmax<<<(P + 255) / 256, 256, 0, st>>>(ws, P);
+        k_inv_minmax<<<g, 256, 0, st>>>(cam, pr, src_depth, src_depth_stride, tgt_depth, H, W, ws);
+    }
+    k_inverse_warp<<<g, 256, 0, st>>>(cam, pr, src_img, src_depth, src_depth_stride, src_bg, tgt_depth, H, W, bandwidth, thr_depth,
+                                      thr_depth_strict, *out, ws);
+    return check_cuda(cudaGetLastError(), "inverse_warp_batched launches");
+}
+
+int syn3r_consistency_batched(const float *depth1, const float *depth2, const float *K1, const float *K1inv,
+                              const float *K2, const float *pair_T, const int32_t *pair_1, const int32_t *pair_2,
+                              int P, int H, int W, float *err, void *stream) {
+    SYN3R_REQUIRE(depth1 && depth2 && K1 && K1inv && K2 && pair_T && pair_1 && pair_2 && err,
+                  "null required pointer");
+    SYN3R_REQUIRE(P > 0 && H > 0 && W > 0, "non-positive size");
+    int rc = check_device();
+    if (rc != SYN3R_OK) return rc;
+    CamF32 cam = make_cam(K1, K1inv, K2, H, W);
+    k_consistency<<<stride_grid2((size_t)H * W, 256, P), 256, 0, (cudaStream_t)stream>>>(cam, pair_T, pair_1, pair_2,
+                                                                                         depth1, depth2, H, W, err);
+    return check_cuda(cudaGetLastError(), "k_consistency");
+}
+
+int syn3r_points_from_depth(const float *depth, const float *Kinv, int H, int W, float *pts, void *stream) {
+    SYN3R_REQUIRE(depth && Kinv && pts, "null required pointer");
+    SYN3R_REQUIRE(H > 0 && W > 0, "non-positive size");
+    int rc = check_device();
+    if (rc != SYN3R_OK) return rc;
+    CamF32 cam = make_cam(Kinv, Kinv, Kinv, H, W);
+    k_points_from_depth<<<stride_grid2((size_t)H * W, 256, 1), 256, 0, (cudaStream_t)stream>>>(depth, cam, H, W, pts);
+    return check_cuda(cudaGetLastError(), "k_points_from_depth");
+}
+
+int syn3r_transform_points(const float *pts, const float *T, int H, int W, float *out, void *stream) {
+    SYN3R_REQUIRE(pts && T && out, "null required pointer");
+    SYN3R_REQUIRE(H > 0 && W > 0, "non-positive size");
+    int rc = check_device();
+    if (rc != SYN3R_OK) return rc;
+    Mat4F32 m;
+    memcpy(m.m, T, sizeof(m.m));
+    k_transform_points<<<stride_grid2((size_t)H * W, 256, 1), 256, 0, (cudaStream_t)stream>>>(pts, m, (size_t)H * W,
+                                                                                              out);
+    return check_cuda(cudaGetLastError(), "k_transform_points");
+}
+
+}  // extern "C"

@@ -1,0 +1,150 @@
+"""Whole-trajectory geometric conditioning: S posed RGB-D sources -> T target poses in one batched call.
+
+This is the batched form of the per-frame Python loops of the reference
+(/root/reference/model/diffusionGS.py:1554-1599 `warp_images`, :1415-1493 `warp_images_bw`): every
+(source, target) pair is one `forward_warp` call (PAIR mode, reference semantics) plus one
+`inverse_warp`-style consistency check, all pairs in a handful of kernel launches.
+
+`TrajectoryWarp` owns the device buffers (inputs, outputs, workspace) and pinned host staging, so a
+step is: H2D of the step's inputs -> kernels -> D2H of the results, with nothing allocated per step.
+"""
+from __future__ import annotations
+
+import dataclasses
+from typing import Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import warp as _w
+
+
+@dataclasses.dataclass
+class TrajectoryOutputs:
+    rgb_f32: Optional[torch.Tensor]       # [P,H,W,3] f32  normalised warped colour (0..255 scale)
+    rgb_u8: Optional[torch.Tensor]        # [P,H,W,3] u8
+    mask: torch.Tensor                    # [P,H,W]   u8   hole mask (1 = covered)
+    winner: Optional[torch.Tensor]        # [P,H,W]   i32  winning source pixel, -1 = hole
+    mask_reproj: Optional[torch.Tensor]   # [P,H,W]   u8   reprojection-consistency mask
+    soft_mask_reproj: Optional[torch.Tensor]  # [P,H,W] f32
+    status: torch.Tensor                  # [P] i32
+
+
+class TrajectoryWarp:
+    """Device-resident plan for one trajectory shape (S sources, pairs, H, W)."""
+
+    def __init__(self, S: int, T: int, H: int, W: int, pair_src: Sequence[int], pair_tgt: Sequence[int], *,
+                 device=None, consistency: bool = True, want_f32: bool = True, want_u8: bool = False,
+                 want_winner: bool = True, bandwidth: float = 20.0, pinned_host: bool = False):
+        self.S, self.T, self.H, self.W = S, T, H, W
+        self.pair_src_h = np.asarray(pair_src, np.int32)
+        self.pair_tgt_h = np.asarray(pair_tgt, np.int32)
+        self.P = len(self.pair_src_h)
+        self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.consistency, self.bandwidth = consistency, float(bandwidth)
+        self.want_f32, self.want_u8, self.want_winner = want_f32, want_u8, want_winner
+        d, P = self.dev, self.P
+        self.rgbd = torch.empty((S, H, W, 4), dtype=torch.float32, device=d)
+        self.tgt_depth = torch.empty((T, H, W), dtype=torch.float32, device=d) if consistency else None
+        self.Kinv_src = torch.empty((S, 9), dtype=torch.float64, device=d)
+        self.pair_par = torch.empty((P, 24), dtype=torch.float64, device=d)
+        self.pair_P = torch.empty((P, 2, 16), dtype=torch.float32, device=d) if consistency else None
+        self.pair_src = torch.from_numpy(self.pair_src_h).to(d)
+        self.pair_tgt = torch.from_numpy(self.pair_tgt_h).to(d)
+        self.K_host = None
+        self.out_fwd = {}
+        self.out_inv = {}
+        # outputs (allocated once)
+        if want_f32:
+            self.out_fwd["rgb_f32"] = torch.empty((P, H, W, 3), dtype=torch.float32, device=d)
+        if want_u8:
+            self.out_fwd["rgb_u8"] = torch.empty((P, H, W, 3), dtype=torch.uint8, device=d)
+        self.out_fwd["mask"] = torch.empty((P, H, W), dtype=torch.uint8, device=d)
+        if want_winner:
+            self.out_fwd["winner"] = torch.empty((P, H, W), dtype=torch.int32, device=d)
+        self.out_fwd["status"] = torch.empty((P,), dtype=torch.int32, device=d)
+        if consistency:
+            self.out_inv["mask_reproj"] = torch.empty((P, H, W), dtype=torch.uint8, device=d)
+            self.out_inv["soft_mask_reproj"] = torch.empty((P, H, W), dtype=torch.float32, device=d)
+        self.pinned = None
+        if pinned_host:
+            self._alloc_pinned()
+
+    # ---- sizes ---------------------------------------------------------------------------------
+    def algorithmic_bytes(self) -> int:
+        """inputs once + outputs once, accumulators zero."""
+        hw = self.H * self.W
+        out_px = (12 if self.want_f32 else 0) + (3 if self.want_u8 else 0) + 1 + (4 if self.want_winner else 0)
+        b = self.S * hw * 16 + self.P * hw * out_px
+        if self.consistency:
+            b += self.T * hw * 4 + self.P * hw * 5
+        return b
+
+    # ---- parameters ----------------------------------------------------------------------------
+    def set_cameras(self, pose_src, pose_tgt, K, K_tgt=None):
+        """Host-side small-matrix preparation + upload (poses in the caller's dtype, K f64 3x3 or [S,3,3])."""
+        Kinv, par = _w.forward_pair_params(pose_src, pose_tgt, K, K_tgt, self.pair_src_h, self.pair_tgt_h)
+        self.Kinv_src.copy_(torch.from_numpy(Kinv))
+        self.pair_par.copy_(torch.from_numpy(par))
+        if self.consistency:
+            K2d = np.asarray(K)
+            assert K2d.ndim == 2, "the backward path shares one K between all views (forward_warp.py:187)"
+            self.K_host = K2d.astype(np.float32)
+            self.pair_P.copy_(torch.from_numpy(
+                _w.inverse_pair_params(pose_src, pose_tgt, self.pair_src_h, self.pair_tgt_h)))
+
+    # ---- data ----------------------------------------------------------------------------------
+    def _alloc_pinned(self):
+        S, T, H, W, P = self.S, self.T, self.H, self.W, self.P
+        pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)  # noqa: E731
+        self.pinned = {"rgbd": pin((S, H, W, 4), torch.float32)}
+        if self.consistency:
+            self.pinned["tgt_depth"] = pin((T, H, W), torch.float32)
+        for k, v in {**self.out_fwd, **self.out_inv}.items():
+            self.pinned["out_" + k] = pin(tuple(v.shape), v.dtype)
+
+    def upload(self, rgbd_host: torch.Tensor, tgt_depth_host: Optional[torch.Tensor] = None):
+        """Async H2D of one step's inputs (pinned host tensors recommended)."""
+        self.rgbd.copy_(rgbd_host, non_blocking=True)
+        if self.consistency:
+            self.tgt_depth.copy_(tgt_depth_host, non_blocking=True)
+
+    def h2d_bytes(self) -> int:
+        return self.rgbd.numel() * 4 + (self.tgt_depth.numel() * 4 if self.consistency else 0)
+
+    def d2h_bytes(self) -> int:
+        return sum(v.numel() * v.element_size() for v in {**self.out_fwd, **self.out_inv}.values())
+
+    def download(self):
+        """Async D2H of every output into the pinned staging buffers."""
+        assert self.pinned is not None, "construct with pinned_host=True"
+        for k, v in {**self.out_fwd, **self.out_inv}.items():
+            self.pinned["out_" + k].copy_(v, non_blocking=True)
+        return self.pinned
+
+    # ---- the hot path --------------------------------------------------------------------------
+    def run(self) -> TrajectoryOutputs:
+        """Enqueue forward warp (+ consistency masks) for all pairs on the current stream."""
+        _w.forward_warp_batched(self.rgbd, self.Kinv_src, self.pair_par, self.pair_src, want_f32=self.want_f32,
+                                want_u8=self.want_u8, want_winner=self.want_winner, is_image=True, out=self.out_fwd)
+        if self.consistency:
+            _w.inverse_warp_batched(None, None, self.tgt_depth, self.K_host, self.pair_P, self.pair_src,
+                                    self.pair_tgt, rgbd=self.rgbd, bandwidth=self.bandwidth,
+                                    want=("mask_reproj", "soft_mask_reproj"), out=self.out_inv)
+        f, i = self.out_fwd, self.out_inv
+        return TrajectoryOutputs(f.get("rgb_f32"), f.get("rgb_u8"), f["mask"], f.get("winner"),
+                                 i.get("mask_reproj"), i.get("soft_mask_reproj"), f["status"])
+
+    def launches_per_run(self) -> int:
+        """Kernels of libsyn3r_warp.so per run() (memsets not counted)."""
+        return 3 + (1 if self.consistency else 0)
+
+
+def from_synth(traj, pairs=None, **kw) -> TrajectoryWarp:
+    """Plan + cameras for a `syn3r_b200.synth.Trajectory`; data is uploaded by the caller."""
+    from . import synth
+    S, T, H, W = traj.shape
+    ps, pt = synth.all_pairs(S, T) if pairs is None else pairs
+    tw = TrajectoryWarp(S, T, H, W, ps, pt, **kw)
+    tw.set_cameras(traj.pose_src, traj.pose_tgt, traj.K)
+    return tw
