@@ -27,12 +27,13 @@ def get_points_from_depth(depth, intrinsics):
     dev = _device()
     h, w = depth.shape
     Kinv = torch.inverse(torch.as_tensor(intrinsics).detach().float().cpu())
-    _, kp = arr = nat.host_f32(Kinv.numpy())
+    karr, kp = nat.host_f32(Kinv.numpy())      # karr keeps the host buffer alive across the call
+    d = _f32(depth, dev)
     pts = torch.empty((h, w, 3), dtype=torch.float32, device=dev)
-    rc = nat.lib().syn3r_points_from_depth(nat.ptr(_f32(depth, dev)), kp, h, w, nat.ptr(pts),
+    rc = nat.lib().syn3r_points_from_depth(nat.ptr(d), kp, h, w, nat.ptr(pts),
                                            torch.cuda.current_stream().cuda_stream)
     nat.check(rc, "syn3r_points_from_depth")
-    del arr
+    del karr
     return pts
 
 
@@ -42,12 +43,13 @@ def transform_points(pts, pose1, pose2):
     h, w, _ = pts.shape
     p1 = torch.as_tensor(pose1).detach().float().cpu()
     p2 = torch.as_tensor(pose2).detach().float().cpu()
-    _, tp = arr = nat.host_f32((p2 @ torch.inverse(p1)).numpy())
+    tarr, tp = nat.host_f32((p2 @ torch.inverse(p1)).numpy())
+    src = _f32(pts, dev)
     out = torch.empty((h, w, 3), dtype=torch.float32, device=dev)
-    rc = nat.lib().syn3r_transform_points(nat.ptr(_f32(pts, dev)), tp, h, w, nat.ptr(out),
+    rc = nat.lib().syn3r_transform_points(nat.ptr(src), tp, h, w, nat.ptr(out),
                                           torch.cuda.current_stream().cuda_stream)
     nat.check(rc, "syn3r_transform_points")
-    del arr
+    del tarr
     return out
 
 

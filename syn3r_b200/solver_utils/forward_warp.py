@@ -59,7 +59,8 @@ def compute_transformed_points(depth1: np.ndarray, transformation1: np.ndarray, 
     d = _up(np.asarray(depth1), torch.float64)
     q = torch.empty((h, w, 3), dtype=torch.float64, device=d.device)
     X = torch.empty_like(q)
-    rc = nat.lib().syn3r_compute_transformed_points(nat.ptr(d), nat.ptr(_up(Kinv)), nat.ptr(_up(par)), h, w,
+    kinv_d, par_d = _up(Kinv), _up(par)        # keep alive until the launch is enqueued
+    rc = nat.lib().syn3r_compute_transformed_points(nat.ptr(d), nat.ptr(kinv_d), nat.ptr(par_d), h, w,
                                                     nat.ptr(q), nat.ptr(X), torch.cuda.current_stream().cuda_stream)
     nat.check(rc, "syn3r_compute_transformed_points")
     return q.cpu().numpy()[..., None], X.cpu().numpy()[..., None]
