@@ -70,6 +70,22 @@ int syn3r_inverse_warp_batched(const float *src_img, const float *src_depth, int
     InvPairs pr{pair_P, pair_src, pair_tgt};
     const size_t hw = (size_t)H * W;
     dim3 g = stride_grid2(hw, 256, P);
+    const bool lean = !need_minmax && !out->warped_img && !out->warped_depth && !out->warped_bg &&
+                      (out->mask_reproj || out->soft_mask_reproj || out->reproj_err);
+    if (lean) {
+        // trajectory hot path: only the consistency-side outputs -> the register-resident specialisation
+        SYN3R_REQUIRE(P <= 65535, "lean path: at most 65535 pairs per call");
+        dim3 gl((W + SYN3R_RM_COLS - 1) / SYN3R_RM_COLS, (H + SYN3R_RM_ROWS - 1) / SYN3R_RM_ROWS, P);
+        if (src_depth_stride == 4)
+            k_reproj_masks<4><<<gl, SYN3R_RM_COLS, 0, st>>>(cam, pr, src_depth, tgt_depth, H, W, bandwidth,
+                                                            out->mask_reproj, out->soft_mask_reproj, out->reproj_err,
+                                                            out->mask_warp);
+        else
+            k_reproj_masks<1><<<gl, SYN3R_RM_COLS, 0, st>>>(cam, pr, src_depth, tgt_depth, H, W, bandwidth,
+                                                            out->mask_reproj, out->soft_mask_reproj, out->reproj_err,
+                                                            out->mask_warp);
+        return check_cuda(cudaGetLastError(), "k_reproj_masks");
+    }
     if (need_minmax) {
         k_inv_init_minmax<<<(P + 255) / 256, 256, 0, st>>>(ws, P);
         k_inv_minmax<<<g, 256, 0, st>>>(cam, pr, src_depth, src_depth_stride, tgt_depth, H, W, ws);

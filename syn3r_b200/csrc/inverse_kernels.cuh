@@ -202,6 +202,112 @@ k_inverse_warp(CamF32 c, InvPairs pr, const float *__restrict__ src_img, const f
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Lean specialisation for the trajectory hot path: only the outputs the reference's callers consume
+// from the consistency side (mask_reproj, soft_mask_reproj; optionally mask_warp / reproj_err;
+// model/diffusionGS.py:758,1346-1347,1486-1487).  Same arithmetic, same op order and therefore the
+// same bits as k_inverse_warp, but organised for instruction count: one thread owns a pixel COLUMN
+// of a (pair, 128 x ROWS) tile, the pair's two 4x4 matrices live in registers, everything that only
+// depends on x (or on y) is hoisted, the homogeneous divide is skipped when w == 1.0f exactly
+// (x / 1.0f == x for every x, NaN included) and Y2/Y2 is formed without a division.
+// ---------------------------------------------------------------------------------------------
+#define SYN3R_RM_ROWS 8
+#define SYN3R_RM_COLS 128
+
+template <int DS>
+__device__ __forceinline__ float tap_ds(const float *__restrict__ img, int H, int W, int yy, int xx) {
+    return ((unsigned)yy < (unsigned)H && (unsigned)xx < (unsigned)W) ? __ldg(img + (size_t)(yy * W + xx) * DS) : 0.0f;
+}
+
+template <int DS>
+__global__ void __launch_bounds__(SYN3R_RM_COLS)
+k_reproj_masks(CamF32 c, InvPairs pr, const float *__restrict__ src_depth, const float *__restrict__ tgt_depth,
+               int H, int W, float bandwidth, uint8_t *__restrict__ o_mask_reproj, float *__restrict__ o_soft,
+               float *__restrict__ o_err, uint8_t *__restrict__ o_mask_warp) {
+    const int p = blockIdx.z, s = pr.pair_src[p], t = pr.pair_tgt[p];
+    const int x = blockIdx.x * SYN3R_RM_COLS + threadIdx.x;
+    const int y0 = blockIdx.y * SYN3R_RM_ROWS;
+    const size_t hw = (size_t)H * W;
+    __shared__ float s_yn[SYN3R_RM_ROWS];
+    const float fx = c.K1[0], fy = c.K1[4], cx = c.K1[2], cy = c.K1[5];      // forward_warp.py:198-201
+    if (threadIdx.x < SYN3R_RM_ROWS)
+        s_yn[threadIdx.x] = __fdiv_rn(__fsub_rn((float)(y0 + threadIdx.x), cy), fy);   // :209, per row
+    __syncthreads();
+    if (x >= W) return;
+    float A[16], B[16];          // A = pose1 @ inv(pose2)  (:217; also T12 of consistency.py:39), B = its inverse pair
+    {
+        const float4 *Pm = reinterpret_cast<const float4 *>(pr.pair_P + (size_t)p * 32);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            float4 a = __ldg(Pm + k), b = __ldg(Pm + 4 + k);
+            A[4 * k] = a.x; A[4 * k + 1] = a.y; A[4 * k + 2] = a.z; A[4 * k + 3] = a.w;
+            B[4 * k] = b.x; B[4 * k + 1] = b.y; B[4 * k + 2] = b.z; B[4 * k + 3] = b.w;
+        }
+    }
+    const float *sd = src_depth + (size_t)s * hw * DS;
+    const float *td = tgt_depth + (size_t)t * hw;
+    const float xf = (float)x;
+    const float xn = __fdiv_rn(__fsub_rn(xf, cx), fx);                        // :208
+    const float kx0 = __fmul_rn(c.K1inv[0], xf), kx1 = __fmul_rn(c.K1inv[3], xf), kx2 = __fmul_rn(c.K1inv[6], xf);
+    const float Wf = (float)W, Hf = (float)H;
+    const int rows = min(SYN3R_RM_ROWS, H - y0);
+    for (int r = 0; r < rows; ++r) {
+        const int y = y0 + r;
+        const float yf = (float)y;
+        const size_t i = (size_t)y * W + x;
+        const float z = __ldg(td + i);
+        // ---- A.2 steps 3-7: where the target pixel falls in the source view -> mask_warp (:233) -----
+        const float c0 = __fmul_rn(xn, z), c1 = __fmul_rn(s_yn[r], z);
+        const float Q0 = dot4_t(A + 0, c0, c1, z, 1.0f), Q1 = dot4_t(A + 4, c0, c1, z, 1.0f),
+                    Q2 = dot4_t(A + 8, c0, c1, z, 1.0f);
+        const float xs = __fadd_rn(__fdiv_rn(__fmul_rn(fx, Q0), Q2), cx);    // :222-223
+        const float ys = __fadd_rn(__fdiv_rn(__fmul_rn(fy, Q1), Q2), cy);
+        const bool mw = (xs >= 0.0f) && (xs < Wf) && (ys >= 0.0f) && (ys < Hf);
+        // ---- A.3: round trip target -> source -> target ------------------------------------------------
+        float X0 = __fmul_rn(__fmaf_rn(c.K1inv[2], 1.0f, __fmaf_rn(c.K1inv[1], yf, kx0)), z);   // consistency.py:58
+        float X1 = __fmul_rn(__fmaf_rn(c.K1inv[5], 1.0f, __fmaf_rn(c.K1inv[4], yf, kx1)), z);
+        float X2 = __fmul_rn(__fmaf_rn(c.K1inv[8], 1.0f, __fmaf_rn(c.K1inv[7], yf, kx2)), z);
+        float Y0 = dot4_t(A + 0, X0, X1, X2, 1.0f), Y1 = dot4_t(A + 4, X0, X1, X2, 1.0f),
+              Y2 = dot4_t(A + 8, X0, X1, X2, 1.0f);
+        const float w = dot4_t(A + 12, X0, X1, X2, 1.0f);                                        // :37-40
+        if (w != 1.0f) { Y0 = __fdiv_rn(Y0, w); Y1 = __fdiv_rn(Y1, w); Y2 = __fdiv_rn(Y2, w); }
+        const float p0 = dot3_t(c.K2 + 0, Y0, Y1, Y2), p1 = dot3_t(c.K2 + 3, Y0, Y1, Y2),
+                    p2 = dot3_t(c.K2 + 6, Y0, Y1, Y2);                                           // :67-68
+        const float u2 = __fdiv_rn(p0, p2), v2 = __fdiv_rn(p1, p2);
+        const float gx = __fsub_rn(__fdiv_rn(u2, c.half_wm1), 1.0f);                             // :71-73
+        const float gy = __fsub_rn(__fdiv_rn(v2, c.half_hm1), 1.0f);
+        const float ix = unnorm(gx, c.half_w), iy = unnorm(gy, c.half_h);                        // :76 (N6)
+        const float xw = floorf(ix), yn_ = floorf(iy);
+        const float we = __fsub_rn(ix, xw), ee = __fsub_rn(1.0f, we), nn = __fsub_rn(iy, yn_), ss = __fsub_rn(1.0f, nn);
+        const int ixw = to_i32(xw), iyn = to_i32(yn_);
+        const int ixe = (ixw == INT_MIN) ? INT_MIN : ixw + 1, iys = (iyn == INT_MIN) ? INT_MIN : iyn + 1;
+        float d12 = __fmul_rn(tap_ds<DS>(sd, H, W, iyn, ixw), __fmul_rn(ss, ee));
+        d12 = __fmaf_rn(tap_ds<DS>(sd, H, W, iyn, ixe), __fmul_rn(ss, we), d12);
+        d12 = __fmaf_rn(tap_ds<DS>(sd, H, W, iys, ixw), __fmul_rn(nn, ee), d12);
+        d12 = __fmaf_rn(tap_ds<DS>(sd, H, W, iys, ixe), __fmul_rn(nn, we), d12);
+        // :79 — (X2 / X2.z) * d12; Y2/Y2 is 1 for finite non-zero Y2 and NaN otherwise
+        const float Z0 = __fmul_rn(__fdiv_rn(Y0, Y2), d12), Z1 = __fmul_rn(__fdiv_rn(Y1, Y2), d12);
+        const float aY2 = fabsf(Y2);
+        const float Z2 = (aY2 > 0.0f && aY2 < CUDART_INF_F) ? d12 : CUDART_NAN_F;
+        float B0 = dot4_t(B + 0, Z0, Z1, Z2, 1.0f), B1 = dot4_t(B + 4, Z0, Z1, Z2, 1.0f),
+              B2 = dot4_t(B + 8, Z0, Z1, Z2, 1.0f);
+        const float w1 = dot4_t(B + 12, Z0, Z1, Z2, 1.0f);                                       // :80
+        if (w1 != 1.0f) { B0 = __fdiv_rn(B0, w1); B1 = __fdiv_rn(B1, w1); B2 = __fdiv_rn(B2, w1); }
+        const float r0 = dot3_t(c.K1 + 0, B0, B1, B2), r1 = dot3_t(c.K1 + 3, B0, B1, B2),
+                    r2 = dot3_t(c.K1 + 6, B0, B1, B2);                                           // :82-83
+        const float ex = __fsub_rn(__fdiv_rn(r0, r2), xf), ey = __fsub_rn(__fdiv_rn(r1, r2), yf);
+        const float e = __fsqrt_rn(__fmaf_rn(ey, ey, __fmul_rn(ex, ex)));                        // :86-89
+        const size_t q = (size_t)p * hw + i;
+        if (o_err) o_err[q] = e;
+        if (o_mask_warp) o_mask_warp[q] = mw;
+        if (o_mask_reproj) o_mask_reproj[q] = (e < bandwidth) && mw;                             // forward_warp.py:260,267
+        if (o_soft) {
+            const float rr = __fdiv_rn(e, bandwidth);
+            o_soft[q] = expf(-__fmul_rn(__fmul_rn(rr, rr), rr));                                 // :265
+        }
+    }
+}
+
 // consistency_check_with_depth (consistency.py:44-91) batched.
 __global__ void __launch_bounds__(256)
 k_consistency(CamF32 c, const float *__restrict__ pair_T, const int *__restrict__ pair_1,
