@@ -267,8 +267,8 @@ def run_ours(args):
 
     kern = {}
     n_k = max(3, min(args.steps, 10))
-    for name, fn in (("fwd_init+zmax", phase(nat.FWD_PHASE_ZMAX)), ("fwd_splat", phase(nat.FWD_PHASE_SPLAT)),
-                     ("fwd_resolve", phase(nat.FWD_PHASE_RESOLVE)), ("inverse_consistency", inv)):
+    for name, fn in (("fwd_prep(stats+zmax+boxes)", phase(nat.FWD_PHASE_ZMAX)),
+                     ("fwd_tile(splat+resolve)", phase(nat.FWD_PHASE_SPLAT)), ("inverse_consistency", inv)):
         kern[name] = statistics.mean(timed(fn, n_k, between=flush.zero_))
     ksum = sum(kern.values())
     dominant = max(kern, key=kern.get)
@@ -284,8 +284,8 @@ def run_ours(args):
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": None, "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback",
                 "algorithmic_bytes_per_step": b_alg,
-                "scope": "all kernels of one step (init+zmax, splat, resolve, inverse); SURVEY 8d B_alg / their summed "
-                         "event time",
+                "scope": "all kernels of one step (block stats, zmax+boxes, tile splat+resolve, reprojection masks); "
+                         "SURVEY 8d B_alg / their summed event time",
                 "dominant_kernel": dominant, "kernel_ms": kern,
                 "kernel_share": {k: v / ksum for k, v in kern.items()}}
 

@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SYN3R_ABI_VERSION 3
+#define SYN3R_ABI_VERSION 4
 
 enum {
     SYN3R_OK = 0,
@@ -47,18 +47,28 @@ enum {
     SYN3R_FWD_GATE_0P6 = 1 << 0, /* mask &= (sum of weights <= 0.6): model/SVD_1pass.py:853-855         */
     SYN3R_FWD_WINNER = 1 << 1,   /* emit the deterministic winner index (extension, 64-bit atomicMin)   */
     SYN3R_FWD_IS_IMAGE = 1 << 2, /* range check + clip[0,255] + round-half-even (forward_warp.py:119-128)*/
-    SYN3R_FWD_FAST_WEIGHT = 1 << 3 /* soft-depth weight via the short fp64 polynomial path (rel. err
-                                      < 1e-9: masks unchanged, colours far inside 1e-5); without it
-                                      the weight uses IEEE log/exp/div like the reference            */
+    SYN3R_FWD_EXACT_WEIGHT = 1 << 3, /* soft-depth weight with IEEE log / exp / div like the reference.  Default:
+                                      a short fp64 table+polynomial path, relative error < 3e-7 (masks and
+                                      winners unchanged, colours move by < 3e-7 of full scale)            */
+    SYN3R_FWD_LEGACY_GLOBAL = 1 << 4 /* first-generation path: global fp32 accumulators + REDG, separate
+                                      resolve pass; kept for A/B measurements.  Default: per-tile
+                                      shared-memory accumulators resolved in place (forward_tile.cuh)     */
     /* measurement aid: run only the named phase(s) of syn3r_forward_warp_batched so a caller can
        bracket each kernel with its own CUDA events; no bit set = all three phases */
-    , SYN3R_FWD_PHASE_ZMAX = 1 << 8    /* workspace init + per-pair max z' reduction */
+    , SYN3R_FWD_PHASE_ZMAX = 1 << 8    /* workspace init, block statistics, per-pair max z' + cell boxes */
     , SYN3R_FWD_PHASE_SPLAT = 1 << 9   /* project + splat                             */
-    , SYN3R_FWD_PHASE_RESOLVE = 1 << 10 /* normalise + masks + winner                  */
+    , SYN3R_FWD_PHASE_RESOLVE = 1 << 10 /* normalise + masks + winner (legacy path only; fused otherwise) */
 };
 
 int syn3r_version(void);
 const char *syn3r_last_error(void);
+
+/* Device self-test: the shared-reciprocal double division used by the forward projection (two quotients
+ * over one denominator) against div.rn.f64 on n pseudo-random operand triples; adds the number of
+ * differing quotients to *mismatches (device u64, caller-zeroed).  mode 0: moderate exponents,
+ * mode 1: arbitrary bit patterns (denormals, inf, NaN included). */
+int syn3r_selftest_ddiv2(unsigned long long n, unsigned long long seed, int mode, unsigned long long *mismatches,
+                         void *stream);
 
 /* Number of SMs / max opt-in shared memory of the current device (host query, cached). */
 int syn3r_device_info(int *sm_count, int *smem_optin_bytes, int *cc_major, int *cc_minor);
@@ -84,7 +94,7 @@ int syn3r_device_info(int *sm_count, int *smem_optin_bytes, int *cc_major, int *
  *   out_status  [n_slots]  i32  nullable: bit0 = colour-range assert of :121-125 failed
  *   workspace   >= syn3r_fwd_workspace_bytes(...) bytes, 256-byte aligned
  * ------------------------------------------------------------------------------------------- */
-size_t syn3r_fwd_workspace_bytes(int H, int W, int n_pairs, int n_slots, int flags);
+size_t syn3r_fwd_workspace_bytes(int H, int W, int S, int n_pairs, int n_slots, int flags);
 
 int syn3r_forward_warp_batched(const float *rgbd, const double *depth64, const uint8_t *src_mask,
                                const double *Kinv_src, const double *pair_par, const int32_t *pair_src,

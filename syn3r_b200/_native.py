@@ -16,10 +16,11 @@ CSRC = os.path.join(_HERE, "csrc")
 FWD_GATE_0P6 = 1 << 0
 FWD_WINNER = 1 << 1
 FWD_IS_IMAGE = 1 << 2
-FWD_FAST_WEIGHT = 1 << 3
+FWD_EXACT_WEIGHT = 1 << 3
+FWD_LEGACY_GLOBAL = 1 << 4
 FWD_PHASE_ZMAX, FWD_PHASE_SPLAT, FWD_PHASE_RESOLVE = 1 << 8, 1 << 9, 1 << 10
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 c_void_p, c_int, c_size_t, c_float = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t, ctypes.c_float
 
@@ -39,8 +40,9 @@ class InvOutputs(ctypes.Structure):
 SIGNATURES = {
     "syn3r_version": (c_int, []),
     "syn3r_last_error": (ctypes.c_char_p, []),
+    "syn3r_selftest_ddiv2": (c_int, [ctypes.c_ulonglong, ctypes.c_ulonglong, c_int, c_void_p, c_void_p]),
     "syn3r_device_info": (c_int, [ctypes.POINTER(c_int)] * 4),
-    "syn3r_fwd_workspace_bytes": (c_size_t, [c_int] * 5),
+    "syn3r_fwd_workspace_bytes": (c_size_t, [c_int] * 6),
     "syn3r_forward_warp_batched": (c_int, [c_void_p] * 7 + [c_int] * 6 + [c_void_p] * 7 + [c_size_t, c_void_p]),
     "syn3r_compute_transformed_points": (c_int, [c_void_p] * 3 + [c_int] * 2 + [c_void_p] * 3),
     "syn3r_bilinear_splat": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p] * 5 + [c_size_t, c_void_p]),

@@ -2,7 +2,7 @@
 #include <stdarg.h>
 #include <string.h>
 
-#include "forward_kernels.cuh"
+#include "forward_tile.cuh"
 
 namespace syn3r {
 
@@ -73,34 +73,119 @@ static dim3 stride_grid(size_t n, int per_block, int ny) {
 }
 
 struct FwdWorkspace {
+    // legacy (global accumulator) layout
     float4 *acc;
     unsigned long long *keys;
+    // shared by both layouts
     unsigned long long *zmax;
     int *znan;
+    // tile layout
+    unsigned *counter;
+    BlockStats *stats;
+    CellBox *blk_box, *sb_box;
     size_t bytes, acc_bytes, keys_bytes, small_bytes;
 };
 
-static FwdWorkspace fwd_layout(void *base, int H, int W, int n_pairs, int n_slots, int flags) {
-    FwdWorkspace w;
+static FwdWorkspace fwd_layout(void *base, int H, int W, int S, int n_pairs, int n_slots, int flags) {
+    FwdWorkspace w{};
     size_t hw = (size_t)H * W;
-    w.acc_bytes = align_up((size_t)n_slots * hw * sizeof(float4), 256);
-    w.keys_bytes = (flags & SYN3R_FWD_WINNER) ? align_up((size_t)n_slots * hw * 8, 256) : 0;
-    size_t zb = align_up((size_t)n_pairs * 8, 256), nb = align_up((size_t)n_pairs * 4, 256);
-    w.small_bytes = zb + nb;
     char *b = (char *)base;
-    w.acc = (float4 *)b;
-    w.keys = w.keys_bytes ? (unsigned long long *)(b + w.acc_bytes) : nullptr;
-    w.zmax = (unsigned long long *)(b + w.acc_bytes + w.keys_bytes);
-    w.znan = (int *)(b + w.acc_bytes + w.keys_bytes + zb);
-    w.bytes = w.acc_bytes + w.keys_bytes + w.small_bytes;
+    size_t zb = align_up((size_t)n_pairs * 8, 256), nb = align_up((size_t)n_pairs * 4, 256);
+    if (flags & SYN3R_FWD_LEGACY_GLOBAL) {
+        w.acc_bytes = align_up((size_t)n_slots * hw * sizeof(float4), 256);
+        w.keys_bytes = (flags & SYN3R_FWD_WINNER) ? align_up((size_t)n_slots * hw * 8, 256) : 0;
+        w.small_bytes = zb + nb;
+        w.acc = (float4 *)b;
+        w.keys = w.keys_bytes ? (unsigned long long *)(b + w.acc_bytes) : nullptr;
+        w.zmax = (unsigned long long *)(b + w.acc_bytes + w.keys_bytes);
+        w.znan = (int *)(b + w.acc_bytes + w.keys_bytes + zb);
+        w.bytes = w.acc_bytes + w.keys_bytes + w.small_bytes;
+        return w;
+    }
+    TileGeom g = make_geom(H, W);
+    w.small_bytes = zb + nb + 256;
+    size_t stats_b = align_up((size_t)S * g.nsb * SYN3R_SB_BLOCKS * sizeof(BlockStats), 256);
+    size_t blk_b = align_up((size_t)n_pairs * g.nsb * SYN3R_SB_BLOCKS * sizeof(CellBox), 256);
+    size_t sb_b = align_up((size_t)n_pairs * g.nsb * sizeof(CellBox), 256);
+    w.zmax = (unsigned long long *)b;
+    w.znan = (int *)(b + zb);
+    w.counter = (unsigned *)(b + zb + nb);
+    w.stats = (BlockStats *)(b + w.small_bytes);
+    w.blk_box = (CellBox *)(b + w.small_bytes + stats_b);
+    w.sb_box = (CellBox *)(b + w.small_bytes + stats_b + blk_b);
+    w.bytes = w.small_bytes + stats_b + blk_b + sb_b;
     return w;
 }
 
+template <bool WINNER, bool EXACT>
+static int launch_tile(const TileArgs &ta, int n_items, cudaStream_t st) {
+    static thread_local int configured_dev = -1;
+    const size_t smem = tile_smem_bytes(WINNER);
+    int dev = -1;
+    SYN3R_TRY_CUDA(cudaGetDevice(&dev));
+    if (configured_dev != dev) {
+        SYN3R_TRY_CUDA(cudaFuncSetAttribute(k_fwd_tile<WINNER, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)smem));
+        configured_dev = dev;
+    }
+    int grid = sm_count();
+    if (grid > n_items) grid = n_items;
+    k_fwd_tile<WINNER, EXACT><<<grid, SYN3R_TILE_THREADS, smem, st>>>(ta);
+    return SYN3R_OK;
+}
+
+}  // namespace syn3r
+
+namespace syn3r {
+// self-test of ddiv2_rn against the library division on pseudo-random operands (mode 0: moderate
+// exponents like projected coordinates, mode 1: arbitrary bit patterns incl. denormals, inf, NaN)
+__global__ void k_selftest_ddiv2(unsigned long long n, unsigned long long seed, int mode,
+                                 unsigned long long *__restrict__ mismatches) {
+    unsigned long long bad = 0;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        unsigned long long v[3];
+        unsigned long long x = (i + 1) * 0x9E3779B97F4A7C15ull + seed;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
+            v[k] = x;
+            x += 0x9E3779B97F4A7C15ull;
+        }
+        double d[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            if (mode == 0) {   // sign | exponent in [1023-40, 1023+40] | random mantissa
+                unsigned long long e = 1023 - 40 + (v[k] >> 52) % 81;
+                d[k] = __longlong_as_double((long long)((v[k] & 0x800fffffffffffffull) | (e << 52)));
+            } else {
+                d[k] = __longlong_as_double((long long)v[k]);
+            }
+        }
+        double c0, c1;
+        ddiv2_rn(d[0], d[1], d[2], c0, c1);
+        const double r0 = __ddiv_rn(d[0], d[2]), r1 = __ddiv_rn(d[1], d[2]);
+        const bool same0 = (__double_as_longlong(c0) == __double_as_longlong(r0)) || (c0 != c0 && r0 != r0);
+        const bool same1 = (__double_as_longlong(c1) == __double_as_longlong(r1)) || (c1 != c1 && r1 != r1);
+        bad += (same0 ? 0 : 1) + (same1 ? 0 : 1);
+    }
+    if (bad) atomicAdd(mismatches, bad);
+}
 }  // namespace syn3r
 
 using namespace syn3r;
 
 extern "C" {
+
+int syn3r_selftest_ddiv2(unsigned long long n, unsigned long long seed, int mode, unsigned long long *mismatches,
+                         void *stream) {
+    SYN3R_REQUIRE(mismatches, "null required pointer");
+    int rc = check_device();
+    if (rc != SYN3R_OK) return rc;
+    k_selftest_ddiv2<<<sm_count() * 8, 256, 0, (cudaStream_t)stream>>>(n, seed, mode, mismatches);
+    return check_cuda(cudaGetLastError(), "k_selftest_ddiv2");
+}
+
 
 int syn3r_version(void) { return SYN3R_ABI_VERSION; }
 const char *syn3r_last_error(void) { return g_err; }
@@ -116,9 +201,9 @@ int syn3r_device_info(int *sm, int *smem, int *major, int *minor) {
     return SYN3R_OK;
 }
 
-size_t syn3r_fwd_workspace_bytes(int H, int W, int n_pairs, int n_slots, int flags) {
-    if (H <= 0 || W <= 0 || n_pairs <= 0 || n_slots <= 0) return 0;
-    return fwd_layout(nullptr, H, W, n_pairs, n_slots, flags).bytes;
+size_t syn3r_fwd_workspace_bytes(int H, int W, int S, int n_pairs, int n_slots, int flags) {
+    if (H <= 0 || W <= 0 || S <= 0 || n_pairs <= 0 || n_slots <= 0) return 0;
+    return fwd_layout(nullptr, H, W, S, n_pairs, n_slots, flags).bytes;
 }
 
 int syn3r_forward_warp_batched(const float *rgbd, const double *depth64, const uint8_t *src_mask,
@@ -135,7 +220,8 @@ int syn3r_forward_warp_batched(const float *rgbd, const double *depth64, const u
     SYN3R_REQUIRE(!out_rgb_u8 || (flags & SYN3R_FWD_IS_IMAGE), "out_rgb_u8 needs SYN3R_FWD_IS_IMAGE");
     int rc = check_device();
     if (rc != SYN3R_OK) return rc;
-    FwdWorkspace ws = fwd_layout(workspace, H, W, P, n_slots, flags);
+    SYN3R_REQUIRE(H <= 32767 && W <= 32767, "H and W must fit int16 cell boxes");
+    FwdWorkspace ws = fwd_layout(workspace, H, W, S, P, n_slots, flags);
     if (workspace_bytes < ws.bytes || ((uintptr_t)workspace & 255)) {
         set_error("forward workspace: need %zu bytes, 256-byte aligned (got %zu at %p)", ws.bytes, workspace_bytes,
                   workspace);
@@ -145,6 +231,38 @@ int syn3r_forward_warp_batched(const float *rgbd, const double *depth64, const u
     const size_t hw = (size_t)H * W;
     const int phase_bits = SYN3R_FWD_PHASE_ZMAX | SYN3R_FWD_PHASE_SPLAT | SYN3R_FWD_PHASE_RESOLVE;
     const int phases = (flags & phase_bits) ? (flags & phase_bits) : phase_bits;
+
+    if (!(flags & SYN3R_FWD_LEGACY_GLOBAL)) {
+        // ---- tile path: accumulators stay in shared memory (forward_tile.cuh) ---------------------------
+        const TileGeom g = make_geom(H, W);
+        SYN3R_REQUIRE(P <= 65535 && S <= 65535, "tile path: at most 65535 pairs / sources per call");
+        if (phases & SYN3R_FWD_PHASE_ZMAX) {
+            SYN3R_TRY_CUDA(cudaMemsetAsync(ws.zmax, 0, ws.small_bytes, st));
+            k_src_stats<<<dim3(g.nsb, S), 256, 0, st>>>((const float4 *)rgbd, depth64, g, ws.stats);
+            k_fwd_prep<<<dim3(g.nsb, P), 256, 0, st>>>((const float4 *)rgbd, depth64, Kinv_src, pair_par, pair_src, g,
+                                                       ws.stats, ws.zmax, ws.znan, ws.blk_box, ws.sb_box);
+        }
+        if (phases & SYN3R_FWD_PHASE_SPLAT) {
+            if (!(phases & SYN3R_FWD_PHASE_ZMAX)) SYN3R_TRY_CUDA(cudaMemsetAsync(ws.counter, 0, 256, st));
+            if (out_status) SYN3R_TRY_CUDA(cudaMemsetAsync(out_status, 0, (size_t)n_slots * 4, st));
+            TileArgs ta{(const float4 *)rgbd, depth64, src_mask, Kinv_src, pair_par, pair_src, pair_slot, P, n_slots,
+                        flags, g, ws.zmax, ws.znan, ws.blk_box, ws.sb_box, ws.counter, out_rgb_f32, out_rgb_u8,
+                        out_mask, out_winner, out_status};
+            const int n_items = n_slots * g.ntiles;
+            const bool win = (flags & SYN3R_FWD_WINNER) != 0, exact = (flags & SYN3R_FWD_EXACT_WEIGHT) != 0;
+            int rc2 = win ? (exact ? launch_tile<true, true>(ta, n_items, st) : launch_tile<true, false>(ta, n_items, st))
+                          : (exact ? launch_tile<false, true>(ta, n_items, st) : launch_tile<false, false>(ta, n_items, st));
+            if (rc2 != SYN3R_OK) return rc2;
+            if (out_flow) {
+                SYN3R_REQUIRE(H <= 65535, "flow output: H must be <= 65535");
+                k_fwd_flow<<<dim3((W + 255) / 256, H, P), 256, 0, st>>>((const float4 *)rgbd, depth64, Kinv_src,
+                                                                        pair_par, pair_src, H, W, out_flow);
+            }
+        }
+        return check_cuda(cudaGetLastError(), "forward_warp_batched (tile path) launches");
+    }
+
+    // ---- legacy path: global fp32 accumulators + REDG (kept for A/B measurements) -----------------------
     dim3 g = stride_grid(hw, 256, P);
     if (phases & SYN3R_FWD_PHASE_ZMAX) {
         SYN3R_TRY_CUDA(cudaMemsetAsync(ws.acc, 0, ws.acc_bytes, st));
@@ -193,7 +311,7 @@ int syn3r_bilinear_splat(const float *frame, const uint8_t *mask1, const double 
     SYN3R_REQUIRE(!out_u8 || (flags & SYN3R_FWD_IS_IMAGE), "out_u8 needs SYN3R_FWD_IS_IMAGE");
     int rc = check_device();
     if (rc != SYN3R_OK) return rc;
-    FwdWorkspace ws = fwd_layout(workspace, H, W, 1, 1, flags);
+    FwdWorkspace ws = fwd_layout(workspace, H, W, 1, 1, 1, flags | SYN3R_FWD_LEGACY_GLOBAL);
     if (workspace_bytes < ws.bytes || ((uintptr_t)workspace & 255)) {
         set_error("splat workspace: need %zu bytes, 256-byte aligned (got %zu)", ws.bytes, workspace_bytes);
         return SYN3R_EWORKSPACE;

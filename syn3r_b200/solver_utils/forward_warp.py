@@ -77,7 +77,7 @@ def bilinear_splatting(frame1: np.ndarray, mask1: Optional[np.ndarray], depth1: 
     m1 = None if mask1 is None else _up(np.asarray(mask1).astype(np.uint8))
     fm = None if flow12_mask is None else _up(np.asarray(flow12_mask).astype(np.uint8))
     flags = nat.FWD_IS_IMAGE if is_image else 0
-    ws = _w._workspace(L.syn3r_fwd_workspace_bytes(h, w, 1, 1, flags), dev, "fwd")
+    ws = _w._workspace(L.syn3r_fwd_workspace_bytes(h, w, 1, 1, 1, flags | nat.FWD_LEGACY_GLOBAL), dev, "fwd")
     outs, mask = [], None
     frame_f32 = np.asarray(frame1).astype(np.float32, copy=False)
     for c0 in range(0, c, 3):                       # accumulators hold 3 channels + weight

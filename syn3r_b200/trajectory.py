@@ -136,7 +136,8 @@ class TrajectoryWarp:
                                  i.get("mask_reproj"), i.get("soft_mask_reproj"), f["status"])
 
     def launches_per_run(self) -> int:
-        """Kernels of libsyn3r_warp.so per run() (memsets not counted)."""
+        """Kernels of libsyn3r_warp.so per run() (memsets not counted): k_src_stats, k_fwd_prep, k_fwd_tile
+        (+ k_reproj_masks)."""
         return 3 + (1 if self.consistency else 0)
 
 

@@ -83,12 +83,14 @@ def forward_pair_params(T_src, T_tgt, K_src, K_tgt, pair_src, pair_tgt):
 
 def forward_warp_batched(rgbd, Kinv_src, pair_par, pair_src, *, pair_slot=None, n_slots=None, depth64=None,
                          src_mask=None, want_f32=True, want_u8=True, want_winner=False, want_flow=False,
-                         gate06=False, is_image=True, out=None, phases=0):
+                         gate06=False, is_image=True, out=None, phases=0, exact_weight=False, legacy=False):
     """Launch the forward warp for P pairs.  All array arguments are CUDA tensors:
     rgbd [S,H,W,4] f32, Kinv_src [S,9] f64, pair_par [P,24] f64, pair_src [P] i32,
     pair_slot [P] i32 or None (PAIR mode).  Returns a dict of CUDA tensors
     (rgb_f32 [n,H,W,3], rgb_u8 [n,H,W,3], mask [n,H,W] u8, winner [n,H,W] i32, flow [P,H,W,2] f64,
-    status [n] i32).  `out` may carry preallocated tensors under the same keys."""
+    status [n] i32).  `out` may carry preallocated tensors under the same keys.
+    `exact_weight`: IEEE log/exp/div for the soft depth weight (default: fast fp64 table path, rel. err < 3e-7);
+    `legacy`: first-generation global-accumulator kernels (A/B measurements)."""
     L = nat.lib()
     S, H, W, four = rgbd.shape
     assert four == 4 and rgbd.dtype == torch.float32
@@ -96,7 +98,8 @@ def forward_warp_batched(rgbd, Kinv_src, pair_par, pair_src, *, pair_slot=None, 
     n = P if pair_slot is None else int(n_slots)
     dev = rgbd.device
     flags = (nat.FWD_GATE_0P6 if gate06 else 0) | (nat.FWD_WINNER if want_winner else 0) | \
-            (nat.FWD_IS_IMAGE if is_image else 0) | int(phases)
+            (nat.FWD_IS_IMAGE if is_image else 0) | int(phases) | (nat.FWD_EXACT_WEIGHT if exact_weight else 0) | \
+            (nat.FWD_LEGACY_GLOBAL if legacy else 0)
     o = dict(out or {})
 
     def get(key, want, shape, dtype):
@@ -115,7 +118,7 @@ def forward_warp_batched(rgbd, Kinv_src, pair_par, pair_src, *, pair_slot=None, 
     winner = get("winner", want_winner, (n, H, W), torch.int32)
     flow = get("flow", want_flow, (P, H, W, 2), torch.float64)
     status = get("status", True, (n,), torch.int32)
-    nbytes = L.syn3r_fwd_workspace_bytes(H, W, P, n, flags)
+    nbytes = L.syn3r_fwd_workspace_bytes(H, W, S, P, n, flags)
     ws = _workspace(nbytes, dev, "fwd")
     rc = L.syn3r_forward_warp_batched(
         nat.ptr(rgbd), nat.ptr(depth64), nat.ptr(src_mask), nat.ptr(Kinv_src), nat.ptr(pair_par), nat.ptr(pair_src),

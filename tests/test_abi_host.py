@@ -38,9 +38,12 @@ def test_library_exports_every_declared_symbol():
 def test_workspace_query_is_pure_host_arithmetic():
     L = nat.lib()
     hw = 576 * 1024
-    assert L.syn3r_fwd_workspace_bytes(576, 1024, 75, 75, 0) >= 75 * hw * 16
-    assert L.syn3r_fwd_workspace_bytes(576, 1024, 75, 75, nat.FWD_WINNER) >= 75 * hw * 24
-    assert L.syn3r_fwd_workspace_bytes(0, 1024, 75, 75, 0) == 0
+    leg = nat.FWD_LEGACY_GLOBAL
+    assert L.syn3r_fwd_workspace_bytes(576, 1024, 3, 75, 75, leg) >= 75 * hw * 16
+    assert L.syn3r_fwd_workspace_bytes(576, 1024, 3, 75, 75, leg | nat.FWD_WINNER) >= 75 * hw * 24
+    # tile path: no per-pixel accumulators in global memory, only block statistics and cell boxes
+    assert 0 < L.syn3r_fwd_workspace_bytes(576, 1024, 3, 75, 75, nat.FWD_WINNER) < 4 << 20
+    assert L.syn3r_fwd_workspace_bytes(0, 1024, 3, 75, 75, 0) == 0
     assert L.syn3r_inv_workspace_bytes(75) % 256 == 0
 
 

@@ -162,12 +162,25 @@ def _check_slot(o, i, r, hw_offsets=None):
     assert o["status"][i] == 0
 
 
-@pytest.mark.parametrize("shape,seed", [((3, 4, 60, 80), 21), ((2, 3, 97, 131), 22), ((1, 2, 16, 8), 23)])
-def test_pair_mode_vs_oracle(shape, seed):
+def test_shared_reciprocal_division_is_ieee():
+    """ddiv2_rn (forward_tile.cuh) == div.rn.f64 bit for bit on 2 x 128M random operand triples per mode."""
+    from syn3r_b200 import _native as nat
+    cnt = torch.zeros(1, dtype=torch.int64, device="cuda")
+    for mode in (0, 1):
+        nat.check(nat.lib().syn3r_selftest_ddiv2(1 << 27, 12345 + mode, mode, cnt.data_ptr(),
+                                                 torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    assert int(cnt.item()) == 0
+
+
+@pytest.mark.parametrize("variant", [{}, {"exact_weight": True}, {"legacy": True}])
+@pytest.mark.parametrize("shape,seed", [((3, 4, 60, 80), 21), ((2, 3, 97, 131), 22), ((1, 2, 16, 8), 23),
+                                        ((2, 2, 150, 300), 24)])
+def test_pair_mode_vs_oracle(shape, seed, variant):
     S, T, H, W = shape
     tr = synth.make_trajectory(S, T, H, W, seed=seed, pose_step=1.5)
     ps, pt = synth.all_pairs(S, T)
-    o = _run_pairs(tr, ps, pt)
+    o = _run_pairs(tr, ps, pt, **variant)
     for p, (s, t) in enumerate(zip(ps, pt)):
         r = _oracle_pair(tr, [s], t)
         # oracle winner indices are relative to its own source list: shift to the global source id
@@ -175,11 +188,12 @@ def test_pair_mode_vs_oracle(shape, seed):
         _check_slot(o, p, r)
 
 
-def test_fused_mode_vs_oracle():
+@pytest.mark.parametrize("variant", [{}, {"legacy": True}])
+def test_fused_mode_vs_oracle(variant):
     S, T, H, W = 4, 3, 72, 96
     tr = synth.make_trajectory(S, T, H, W, seed=31, pose_step=1.0)
     ps, pt = synth.all_pairs(S, T)
-    o = _run_pairs(tr, ps, pt, fused=True)
+    o = _run_pairs(tr, ps, pt, fused=True, **variant)
     pair = _run_pairs(tr, ps, pt)
     for t in range(T):
         r = _oracle_pair(tr, list(range(S)), t)
