@@ -51,6 +51,38 @@ __global__ void k_smem(float *out, int iters) {
     if (threadIdx.x == 0) out[blockIdx.x] = sm[5] + sm[4097];
 }
 
+// native 32-bit integer shared atomics (ATOMS.ADD / ATOMS.MAX, no CAS loop)
+template <int OP>  // 0 4x ATOMS.ADD u32, 1 ATOMS.MAX + ATOMS.ADD, 2 4x ATOMS.ADD with 2-way bank conflicts, 3 LDS + 4x ATOMS.ADD
+__global__ void k_smem_int(unsigned *out, int iters) {
+    extern __shared__ unsigned smi[];
+    const int ncell = 8192;
+    for (int i = threadIdx.x; i < ncell; i += blockDim.x) smi[i] = 0u;
+    __syncthreads();
+    unsigned acc = 0;
+    for (int it = 0; it < iters; ++it) {
+        int c = (threadIdx.x + it * 37) & 2047;
+        if (OP == 2) c = ((threadIdx.x * 2) + it * 37) & 2047;
+        unsigned v = (unsigned)it;
+        if (OP == 3) acc += smi[(c + 5) & 2047];
+        if (OP == 0 || OP == 2 || OP == 3) { atomicAdd(smi + c, v); atomicAdd(smi + 2048 + c, v); atomicAdd(smi + 4096 + c, v); atomicAdd(smi + 6144 + c, 1u); }
+        if (OP == 1) { atomicMax(smi + c, v); atomicAdd(smi + 2048 + c, 1u); }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) out[blockIdx.x] = smi[5] + smi[4097] + acc;
+}
+
+// red.v4.f32 into a CTA-private, L2-resident 128 KB window (8192 cells x 16 B), rows of 32 consecutive cells per warp
+template <int OP>  // 0 red.v4.f32, 1 red.v4.f32 x4 corners (2x2 neighbourhood)
+__global__ void k_glob_window(float4 *acc, int iters) {
+    float4 *win = acc + (size_t)blockIdx.x * 8192;
+    for (int it = 0; it < iters; ++it) {
+        int c = (threadIdx.x + it * 37 * 32) & 8191;
+        float v = (float)it;
+        red4(win + c, v, v, v, 1.0f);
+        if (OP == 1) { red4(win + ((c + 1) & 8191), v, v, v, 1.0f); red4(win + ((c + 128) & 8191), v, v, v, 1.0f); red4(win + ((c + 129) & 8191), v, v, v, 1.0f); }
+    }
+}
+
 // fp64 / conversion pipe throughput
 template <int OP>  // 0 DFMA chain x8 independent, 1 F2F.F32.F64 + F2F.F64.F32, 2 FRND floor f64, 3 ddiv, 4 MUFU.RCP64H
 __global__ void k_alu(double *out, int iters, double seed) {
@@ -137,6 +169,35 @@ int main() {
         double l2 = (double)sms * 4 * 256 * it2;
         printf("shared %-18s %8.3f ms  %7.2f Glane-op/s  %6.3f SM-cyc/lane\n", son[op], ms, l2 / ms / 1e6,
                ms * 1e-3 * ghz * 1e9 * sms / l2);
+    }
+    unsigned *uout; CK(cudaMalloc(&uout, 4 * blocks));
+    const char *sin[] = {"4x ATOMS.ADD.u32", "ATOMS.MAX+ATOMS.ADD", "4x ATOMS.ADD 2-way conflict", "LDS + 4x ATOMS.ADD"};
+    for (int op = 0; op < 4; ++op) {
+        const int it2 = 2048;
+        auto run = [&]() {
+            switch (op) {
+                case 0: k_smem_int<0><<<sms * 4, 256, 32768>>>(uout, it2); break;
+                case 1: k_smem_int<1><<<sms * 4, 256, 32768>>>(uout, it2); break;
+                case 2: k_smem_int<2><<<sms * 4, 256, 32768>>>(uout, it2); break;
+                case 3: k_smem_int<3><<<sms * 4, 256, 32768>>>(uout, it2); break;
+            }
+        };
+        float ms = time_ms(run);
+        double l2 = (double)sms * 4 * 256 * it2;
+        printf("shared %-28s %8.3f ms  %7.2f Glane-iter/s  %6.3f SM-cyc/lane-iter\n", sin[op], ms, l2 / ms / 1e6,
+               ms * 1e-3 * ghz * 1e9 * sms / l2);
+    }
+    for (int op = 0; op < 2; ++op) {
+        const int it2 = 512;
+        for (int nb : {sms, sms * 2}) {
+            auto run = [&]() {
+                if (op == 0) k_glob_window<0><<<nb, 512>>>(acc, it2); else k_glob_window<1><<<nb, 512>>>(acc, it2);
+            };
+            float ms = time_ms(run);
+            double l2 = (double)nb * 512 * it2 * (op ? 4 : 1);
+            printf("global red.v4.f32 CTA-private 128 KB window (%s, %d CTAs x 512) %8.3f ms  %7.2f Glane-op/s  %6.3f SM-cyc/lane\n",
+                   op ? "2x2 corners" : "1 cell", nb, ms, l2 / ms / 1e6, ms * 1e-3 * ghz * 1e9 * sms / l2);
+        }
     }
     double *dout; CK(cudaMalloc(&dout, 8));
     const char *aon[] = {"DFMA", "F2F f64<->f32 pair", "floor.f64 (+DMUL)", "ddiv_rn (+DADD)", "rcp.approx.f64 (+DADD)"};
