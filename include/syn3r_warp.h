@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SYN3R_ABI_VERSION 4
+#define SYN3R_ABI_VERSION 5
 
 enum {
     SYN3R_OK = 0,
@@ -50,9 +50,13 @@ enum {
     SYN3R_FWD_EXACT_WEIGHT = 1 << 3, /* soft-depth weight with IEEE log / exp / div like the reference.  Default:
                                       a short fp64 table+polynomial path, relative error < 3e-7 (masks and
                                       winners unchanged, colours move by < 3e-7 of full scale)            */
-    SYN3R_FWD_LEGACY_GLOBAL = 1 << 4 /* first-generation path: global fp32 accumulators + REDG, separate
+    SYN3R_FWD_LEGACY_GLOBAL = 1 << 4, /* first-generation path: global fp32 accumulators + REDG, separate
                                       resolve pass; kept for A/B measurements.  Default: per-tile
-                                      shared-memory accumulators resolved in place (forward_tile.cuh)     */
+                                      shared-memory accumulators resolved in place                         */
+    SYN3R_FWD_FP32_TILE = 1 << 5     /* second-generation path: per-tile fp32 accumulators (CAS atomics,
+                                      forward_tile.cuh); kept for A/B measurements and used automatically for
+                                      tiles the default integer block-floating-point kernel (forward_fx.cuh)
+                                      hands back.  EXACT_WEIGHT implies it                                 */
     /* measurement aid: run only the named phase(s) of syn3r_forward_warp_batched so a caller can
        bracket each kernel with its own CUDA events; no bit set = all three phases */
     , SYN3R_FWD_PHASE_ZMAX = 1 << 8    /* workspace init, block statistics, per-pair max z' + cell boxes */
@@ -88,7 +92,8 @@ int syn3r_device_info(int *sm_count, int *smem_optin_bytes, int *cc_major, int *
  *   out_rgb_u8  [n_slots,H,W,3] u8   nullable: clipped + rounded (:127-128), needs IS_IMAGE
  *   out_mask    [n_slots,H,W]   u8   mask2 (:112), 0/1
  *   out_winner  [n_slots,H,W]   i32  nullable, needs WINNER: src*H*W + y*W + x of the contributing
- *                                     source pixel with the smallest (float)z', ties -> smallest
+ *                                     source pixel with the smallest z' key (high 32 bits of the fp64 z':
+ *                                     sign, exponent, 20 mantissa bits), ties -> smallest
  *                                     index; -1 = hole
  *   out_flow    [P,H,W,2]  f64  nullable: flow12 (:177)
  *   out_status  [n_slots]  i32  nullable: bit0 = colour-range assert of :121-125 failed

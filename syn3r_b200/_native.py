@@ -18,9 +18,10 @@ FWD_WINNER = 1 << 1
 FWD_IS_IMAGE = 1 << 2
 FWD_EXACT_WEIGHT = 1 << 3
 FWD_LEGACY_GLOBAL = 1 << 4
+FWD_FP32_TILE = 1 << 5
 FWD_PHASE_ZMAX, FWD_PHASE_SPLAT, FWD_PHASE_RESOLVE = 1 << 8, 1 << 9, 1 << 10
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 c_void_p, c_int, c_size_t, c_float = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t, ctypes.c_float
 

@@ -2,7 +2,7 @@
 #include <stdarg.h>
 #include <string.h>
 
-#include "forward_tile.cuh"
+#include "forward_fx.cuh"
 
 namespace syn3r {
 
@@ -80,9 +80,11 @@ struct FwdWorkspace {
     unsigned long long *zmax;
     int *znan;
     // tile layout
-    unsigned *counter;
+    unsigned *counter;          // [0] work counter, [16] cmax_bits, [32] redo_count, [48] redo work counter
     BlockStats *stats;
     CellBox *blk_box, *sb_box;
+    PairFast *pair_fast;
+    int *redo_list;
     size_t bytes, acc_bytes, keys_bytes, small_bytes;
 };
 
@@ -110,10 +112,14 @@ static FwdWorkspace fwd_layout(void *base, int H, int W, int S, int n_pairs, int
     w.zmax = (unsigned long long *)b;
     w.znan = (int *)(b + zb);
     w.counter = (unsigned *)(b + zb + nb);
+    size_t pf_b = align_up((size_t)n_pairs * sizeof(PairFast), 256);
+    size_t redo_b = align_up((size_t)n_slots * g.ntiles * sizeof(int), 256);
     w.stats = (BlockStats *)(b + w.small_bytes);
     w.blk_box = (CellBox *)(b + w.small_bytes + stats_b);
     w.sb_box = (CellBox *)(b + w.small_bytes + stats_b + blk_b);
-    w.bytes = w.small_bytes + stats_b + blk_b + sb_b;
+    w.pair_fast = (PairFast *)(b + w.small_bytes + stats_b + blk_b + sb_b);
+    w.redo_list = (int *)(b + w.small_bytes + stats_b + blk_b + sb_b + pf_b);
+    w.bytes = w.small_bytes + stats_b + blk_b + sb_b + pf_b + redo_b;
     return w;
 }
 
@@ -131,6 +137,29 @@ static int launch_tile(const TileArgs &ta, int n_items, cudaStream_t st) {
     int grid = sm_count();
     if (grid > n_items) grid = n_items;
     k_fwd_tile<WINNER, EXACT><<<grid, SYN3R_TILE_THREADS, smem, st>>>(ta);
+    return SYN3R_OK;
+}
+
+// fixed-point kernel, then the fp32 kernel over whatever work items it handed back (normally none)
+template <bool WINNER>
+static int launch_tile_fx(const TileArgs &ta, int n_items, cudaStream_t st) {
+    static thread_local int configured_dev = -1;
+    const size_t smem = fx_smem_bytes(WINNER), smem_redo = tile_smem_bytes(WINNER);
+    int dev = -1;
+    SYN3R_TRY_CUDA(cudaGetDevice(&dev));
+    if (configured_dev != dev) {
+        SYN3R_TRY_CUDA(cudaFuncSetAttribute(k_fwd_tile_fx<WINNER>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)smem));
+        SYN3R_TRY_CUDA(cudaFuncSetAttribute(k_fwd_tile<WINNER, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)smem_redo));
+        configured_dev = dev;
+    }
+    int grid = sm_count();
+    if (grid > n_items) grid = n_items;
+    k_fwd_tile_fx<WINNER><<<grid, SYN3R_TILE_THREADS, smem, st>>>(ta);
+    TileArgs tr = ta;
+    tr.redo_mode = 1;
+    k_fwd_tile<WINNER, false><<<grid, SYN3R_TILE_THREADS, smem_redo, st>>>(tr);
     return SYN3R_OK;
 }
 
@@ -238,20 +267,29 @@ int syn3r_forward_warp_batched(const float *rgbd, const double *depth64, const u
         SYN3R_REQUIRE(P <= 65535 && S <= 65535, "tile path: at most 65535 pairs / sources per call");
         if (phases & SYN3R_FWD_PHASE_ZMAX) {
             SYN3R_TRY_CUDA(cudaMemsetAsync(ws.zmax, 0, ws.small_bytes, st));
-            k_src_stats<<<dim3(g.nsb, S), 256, 0, st>>>((const float4 *)rgbd, depth64, g, ws.stats);
+            k_src_stats<<<dim3(g.nsb, S), 256, 0, st>>>((const float4 *)rgbd, depth64, g, ws.stats, ws.counter + 16);
             k_fwd_prep<<<dim3(g.nsb, P), 256, 0, st>>>((const float4 *)rgbd, depth64, Kinv_src, pair_par, pair_src, g,
-                                                       ws.stats, ws.zmax, ws.znan, ws.blk_box, ws.sb_box);
+                                                       ws.stats, ws.zmax, ws.znan, ws.blk_box, ws.sb_box, ws.pair_fast);
+            k_fwd_finalize<<<(P + 127) / 128, 128, 0, st>>>(ws.zmax, ws.znan, P, ws.pair_fast);
         }
         if (phases & SYN3R_FWD_PHASE_SPLAT) {
-            if (!(phases & SYN3R_FWD_PHASE_ZMAX)) SYN3R_TRY_CUDA(cudaMemsetAsync(ws.counter, 0, 256, st));
+            if (!(phases & SYN3R_FWD_PHASE_ZMAX)) {      // counters only; cmax_bits ([16]) is phase-1 state
+                SYN3R_TRY_CUDA(cudaMemsetAsync(ws.counter, 0, 64, st));
+                SYN3R_TRY_CUDA(cudaMemsetAsync(ws.counter + 32, 0, 128, st));
+            }
             if (out_status) SYN3R_TRY_CUDA(cudaMemsetAsync(out_status, 0, (size_t)n_slots * 4, st));
             TileArgs ta{(const float4 *)rgbd, depth64, src_mask, Kinv_src, pair_par, pair_src, pair_slot, P, n_slots,
                         flags, g, ws.zmax, ws.znan, ws.blk_box, ws.sb_box, ws.counter, out_rgb_f32, out_rgb_u8,
-                        out_mask, out_winner, out_status};
+                        out_mask, out_winner, out_status, ws.pair_fast, ws.counter + 16, ws.redo_list,
+                        ws.counter + 32, ws.counter + 48, 0};
             const int n_items = n_slots * g.ntiles;
             const bool win = (flags & SYN3R_FWD_WINNER) != 0, exact = (flags & SYN3R_FWD_EXACT_WEIGHT) != 0;
-            int rc2 = win ? (exact ? launch_tile<true, true>(ta, n_items, st) : launch_tile<true, false>(ta, n_items, st))
-                          : (exact ? launch_tile<false, true>(ta, n_items, st) : launch_tile<false, false>(ta, n_items, st));
+            const bool fp32acc = (flags & SYN3R_FWD_FP32_TILE) != 0;
+            int rc2;
+            if (exact) rc2 = win ? launch_tile<true, true>(ta, n_items, st) : launch_tile<false, true>(ta, n_items, st);
+            else if (fp32acc || depth64 || src_mask)     // f64 depth / mask1: per-pair API extras, fp32 tile kernel
+                rc2 = win ? launch_tile<true, false>(ta, n_items, st) : launch_tile<false, false>(ta, n_items, st);
+            else rc2 = win ? launch_tile_fx<true>(ta, n_items, st) : launch_tile_fx<false>(ta, n_items, st);
             if (rc2 != SYN3R_OK) return rc2;
             if (out_flow) {
                 SYN3R_REQUIRE(H <= 65535, "flow output: H must be <= 65535");

@@ -78,6 +78,11 @@ __device__ __forceinline__ double unordered_f64(unsigned long long k) {
     return __longlong_as_double((long long)((k >> 63) ? (k & 0x7fffffffffffffffull) : ~k));
 }
 
+// winner depth key (extension output, include/syn3r_warp.h): the high word of the fp64 z' (sign, exponent,
+// 20 mantissa bits), order-preserving.  Truncation instead of a float rounding so that a cheap integer test on
+// the low word tells when two evaluations of z' could disagree on the key.
+__device__ __forceinline__ unsigned zkey_of(double z) { return ordered_u32(__int_as_float(__double2hiint(z))); }
+
 // streaming (read-once / write-once) accesses: keep L1 for the data that is re-used
 __device__ __forceinline__ float4 ld_stream_f4(const float4 *p) {
     float4 r;

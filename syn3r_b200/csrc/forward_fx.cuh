@@ -1,0 +1,515 @@
+// forward_fx.cuh — forward depth warp, target-tile-owned, INTEGER shared-memory accumulation.
+//
+// Why: on sm_100a the only native shared-memory atomics are 32-bit integer ones (ATOMS.ADD / MIN / MAX, one
+// warp instruction per cycle per SM, tools/microbench/atomics.cu); atomicAdd(float) and every 64-bit
+// atomic compile to LDS + ATOMS.CAST.SPIN loops, which is what bounded k_fwd_tile (forward_tile.cuh) at
+// 3.1 ms on the headline workload.  This kernel produces the same outputs with native atomics only.
+//
+// Per work item (output slot, 128x48 target tile), two sweeps over the culled source blocks:
+//   sweep 1   every corner that lands in the tile does  ATOMS.MAX Wmax[cell] <- bits(w)      (w > 0 fp32)
+//             and, for the winner output,               ATOMS.MIN zkey[cell] <- ordered(float z')
+//   sweep 2   the corner's weight is expressed relative to the cell's own power of two,
+//             q = w * 2^(21 - exponent(Wmax[cell])) in (0, 2^22), and accumulated as integers:
+//             S += rint(q), I_c += rint(q * colour_c / cscale)  (4 ATOMS.ADD); the winner index is an
+//             ATOMS.MIN among the corners whose z-key equals the cell's minimum.
+//   resolve   colour = I_c / S * cscale, mask = Wmax > 0, winner; planes are cleared for the next item.
+// A block-floating-point accumulator with a per-cell exponent: the largest contribution of a cell keeps 21-22
+// significant bits, a cell's rounding error is <= N * 2^-22 of full scale for N contributions (typically
+// sqrt(N) * 1e-7), sums are order-independent (bitwise reproducible run to run), and the hole mask does not
+// depend on the accumulation at all.  If a cell's S would pass 2^32 (> 1024 near-maximal contributions) the
+// work item is handed to k_fwd_tile (fp32 CAS accumulation) through a redo list.
+//
+// The projection is evaluated as q = d (A p) + b with the composite A = K2 R K1inv (12 DFMA + one reciprocal
+// per pixel instead of the reference's ~60-operation chain).  Its floor() can differ from the bit-faithful
+// chain only when the coordinate is within the bound k_fwd_prep derives of an
+// integer; such pixels (all of them for an identity pose, ~1e-9 of them for a generic one) take
+// exact_pixel(), which IS the bit-faithful chain.  Cell assignment, hence the hole mask and the set of
+// contributors, is therefore identical to the reference's; weights differ by ~1e-12 relative.
+#pragma once
+#include "forward_tile.cuh"
+
+namespace syn3r {
+
+#define SYN3R_FX_BITS 21
+#define SYN3R_FX_MAGIC 12582912.0f          /* 1.5 * 2^23: low mantissa bits of (v + MAGIC) are rint(v) */
+#define SYN3R_FX_MAGIC_BITS 0x4B400000
+
+// Shared-memory layout: planes of CELLS 32-bit words, addressed as fx_smem[PLANE * CELLS + cell] so that the
+// plane and the corner offset fold into the immediate field of LDS / ATOMS.
+//   WMAX  fp32 bit pattern of the largest corner weight (0 = untouched)     S   sum of rint(q)
+//   I0..2 sum of rint(q * c / cscale)                                       ZKEY, IDX  winner (WINNER only)
+extern __shared__ __align__(16) unsigned fx_smem[];
+enum { FX_WMAX = 0, FX_S = 1, FX_I0 = 2, FX_I1 = 3, FX_I2 = 4, FX_ZKEY = 5, FX_IDX = 6 };
+#define FX_CELLS (SYN3R_TILE_W * SYN3R_TILE_H)
+#define FX_PLANE (SYN3R_TILE_W * (SYN3R_TILE_H + 1))       /* one extra row: per-lane trash cells */
+
+struct FxAux {                  // the rest of the shared memory, behind the planes
+    double2 *logtab;
+    int *listA, *listB, *ctl;
+};
+
+struct PixelGeom {              // where a source pixel lands relative to the tile
+    int lxf, lyf;               // local cell of the floor corner
+    float ax, bx, ay, by;       // proximity factors of the floor / ceil corner per axis (A.1 step 11)
+    bool vx0, vx1, vy0, vy1;    // corner column / row takes part (inside the tile and a distinct cell)
+    double z;                   // z' (:174)
+};
+
+// The bit-faithful chain for one pixel (same code as splat_block_into_tile): out of line, rarely taken.
+__device__ __noinline__ PixelGeom exact_pixel(const double *__restrict__ par_g, const double *__restrict__ Ki_g,
+                                              int x, int y, double d, int tx0, int ty0, int tw, int th) {
+    double par[21], Ki[9];
+#pragma unroll
+    for (int k = 0; k < 21; ++k) par[k] = par_g[k];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) Ki[k] = Ki_g[k];
+    const double xd = (double)x, yd = (double)y;
+    double X0, X1, X2;
+    unproject(Ki, xd, yd, d, X0, X1, X2);
+    const double *M = par, *K2 = par + 12;
+    const double t0 = dot4_blas_h(M + 0, X0, X1, X2), t1 = dot4_blas_h(M + 4, X0, X1, X2),
+                 t2 = dot4_blas_h(M + 8, X0, X1, X2);
+    const double q0 = dot3_blas(K2 + 0, t0, t1, t2), q1 = dot3_blas(K2 + 3, t0, t1, t2),
+                 z = dot3_blas(K2 + 6, t0, t1, t2);
+    double cx, cy;
+    ddiv2_rn(q0, q1, z, cx, cy);
+    const double ox = __dadd_rn(__dadd_rn(__dsub_rn(cx, xd), xd), 1.0);
+    const double oy = __dadd_rn(__dadd_rn(__dsub_rn(cy, yd), yd), 1.0);
+    int xf, xc, yf, yc;
+    PixelGeom g;
+    axis_cells(ox, xf, xc, g.ax, g.bx);
+    axis_cells(oy, yf, yc, g.ay, g.by);
+    g.lxf = xf - tx0; g.lyf = yf - ty0;
+    // an exact-integer landing puts both "corners" on one cell (N3): the ceil corner is not a distinct cell,
+    // its factor (1.0) joins the floor corner's
+    g.vx0 = (unsigned)g.lxf < (unsigned)tw;
+    g.vy0 = (unsigned)g.lyf < (unsigned)th;
+    g.vx1 = (xc != xf) && (unsigned)(g.lxf + 1) < (unsigned)tw;
+    g.vy1 = (yc != yf) && (unsigned)(g.lyf + 1) < (unsigned)th;
+    if (xc == xf) { g.ax = __fadd_rn(g.ax, g.bx); g.bx = 0.0f; }
+    if (yc == yf) { g.ay = __fadd_rn(g.ay, g.by); g.by = 0.0f; }
+    g.z = z;
+    return g;
+}
+
+// Local coordinate SHIFTED BY ONE (v1 = coordinate - tile origin + 1) -> n1 = rint(v1) and the signed remainder
+// f in [-0.5, 0.5] (as fp32), without any conversion instruction on the fp64 side: adding 1.5 * 2^52 leaves
+// rint(v1) in the low word.  For every v1 whose corners can touch the tile n1 is in [0, extent + 1] and the high
+// word is exactly the magic number's; NaN, inf, negative and huge values fail that test.
+__device__ __forceinline__ void rint_split(double v1, int &n1, float &f, bool &hi_ok) {
+    const double t = __dadd_rn(v1, 6755399441055744.0);
+    n1 = __double2loint(t);
+    hi_ok = __double2hiint(t) == 0x43380000;
+    f = __double2float_rn(__dsub_rn(v1, __dsub_rn(t, 6755399441055744.0)));
+}
+
+// 2^90 / dw as in fast_weight_scale (forward_tile.cuh), degree-4 polynomial (|r| < 2^-7: the r^5 term is < 1e-11).
+// `clamp_hi`: the pair's max z' exceeds 5000, so the upper clip of :82 can matter (uniform per pair).
+__device__ __forceinline__ float fx_weight_scale(const double2 *__restrict__ logtab, double cexp, double z,
+                                                 bool clamp_hi) {
+    double v = __dadd_rn(1.0, z);
+    if (__double2hiint(z) < 0) v = 1.0;                                     // clip(z, 0, .): z < 0 or -0.0
+    if (clamp_hi && z > 5000.0) v = 5001.0;
+    const int idx = (__double2hiint(v) - 0x3ff00000) >> 14;
+    const double2 T = logtab[idx];
+    const double r = __fma_rn(v, T.x, -1.0);
+    double p = __fma_rn(r, -0.36067376022224085, 0.48089834696298783);      // -1/(4 ln2), 1/(3 ln2)
+    p = __fma_rn(r, p, -0.72134752044448170);                               // -1/(2 ln2)
+    p = __fma_rn(r, p, 1.4426950408889634);                                 //  1/ln2
+    const double L2 = __fma_rn(r, p, T.y);
+    const double E = __dmul_rn(L2, cexp);                                   // in [0, 72.2]
+    const double t = __dadd_rn(E, 6755399441055744.0);
+    const int n = __double2loint(t);
+    const double f = __dsub_rn(__dsub_rn(t, 6755399441055744.0), E);        // n - E in [-0.5, 0.5]
+    float e2;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e2) : "f"(__double2float_rn(f)));
+    return __fmul_rn(e2, __int_as_float((127 + 90 - n) << 23));
+}
+
+struct FxPairRegs {             // per-pair values a thread keeps in registers over the pair's blocks
+    double A[9], b[3];
+    float k0, k1, k2, k3, k4;
+    double cexp;
+    bool clamp_hi;
+};
+
+struct RowProj {                // fast projection of one source pixel, relative to the tile
+    double q2;                  // z'
+    int nx1, ny1;               // rint(local coordinate + 1)
+    float fx, fy;               // signed remainders in [-0.5, 0.5]
+    bool cand;                  // the floor or the ceil corner can fall inside the tile (decided exactly later)
+};
+
+// tx1d / ty1d = (double)(tile origin - 1)
+__device__ __forceinline__ RowProj fx_project(const FxPairRegs &pr, double u0, double u1, double u2, double yd,
+                                              double d, double tx1d, double ty1d, int tw, int th) {
+    RowProj o;
+    const double q0 = __fma_rn(d, __fma_rn(pr.A[1], yd, u0), pr.b[0]);
+    const double q1 = __fma_rn(d, __fma_rn(pr.A[4], yd, u1), pr.b[1]);
+    o.q2 = __fma_rn(d, __fma_rn(pr.A[7], yd, u2), pr.b[2]);
+    double r0;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r0) : "d"(o.q2));
+    double e = __fma_rn(-o.q2, r0, 1.0);
+    e = __fma_rn(e, e, e);
+    const double rc = __fma_rn(r0, e, r0);                                  // 1/q2, relative error ~2^-58
+    const double lx = __dsub_rn(__dmul_rn(q0, rc), tx1d), ly = __dsub_rn(__dmul_rn(q1, rc), ty1d);
+    bool okx, oky;
+    rint_split(lx, o.nx1, o.fx, okx);
+    rint_split(ly, o.ny1, o.fy, oky);
+    // n1 in [0, extent + 1]  <=>  nearest integer of the local coordinate in [-1, extent]
+    o.cand = okx && oky && (unsigned)o.nx1 <= (unsigned)(tw + 1) && (unsigned)o.ny1 <= (unsigned)(th + 1);
+    return o;
+}
+
+// Everything after the projection for one candidate pixel; SWEEP 1 = per-cell maxima, SWEEP 2 = accumulation.
+// i = s*H*W + y*W + x (the winner index).  Corners that are not part of the tile are sent, with weight 0, to the
+// lane's own cell of the trash row behind the tile, so the four corners run without a branch.
+template <bool WINNER, int SWEEP>
+__device__ __forceinline__ void fx_pixel(const TileArgs &a, const double2 *__restrict__ logtab, const FxPairRegs &pr,
+                                         const RowProj &rp, const float4 px, int p, int s, int x, int y, unsigned i,
+                                         int tx0, int ty0, int tw, int th, float cs_inv, int lane,
+                                         unsigned &ovf_bits) {
+    const float zf = fabsf(__double2float_rn(rp.q2)), df = fabsf(px.w);
+    const float lhs = __fmul_rn(fminf(fabsf(rp.fx), fabsf(rp.fy)), zf);
+    const float rhs = __fmaf_rn(zf, pr.k2, __fmaf_rn(df, pr.k1, pr.k0));
+    bool slow = !(lhs > rhs);
+    if (WINNER) {
+        // z-key = high word of z': ambiguous when the low word is within 2^14 ulps of a carry, or when the
+        // fast z' is not known to 2^-39 relative
+        slow = slow || ((unsigned)__double2loint(rp.q2) + 16384u < 32768u) ||
+               !(__fmul_rn(zf, 1.8e-12f) > __fmaf_rn(df, pr.k3, pr.k4));
+    }
+    PixelGeom g;
+    if (slow) {
+        g = exact_pixel(a.pair_par + (size_t)p * 24, a.Kinv_src + (size_t)s * 9, x, y, (double)px.w, tx0, ty0, tw, th);
+    } else {
+        const bool negx = rp.fx < 0.0f, negy = rp.fy < 0.0f;
+        g.lxf = rp.nx1 - (negx ? 2 : 1); g.lyf = rp.ny1 - (negy ? 2 : 1);
+        g.ax = negx ? -rp.fx : __fsub_rn(1.0f, rp.fx); g.bx = negx ? __fadd_rn(1.0f, rp.fx) : rp.fx;
+        g.ay = negy ? -rp.fy : __fsub_rn(1.0f, rp.fy); g.by = negy ? __fadd_rn(1.0f, rp.fy) : rp.fy;
+        g.vx0 = (unsigned)g.lxf < (unsigned)tw; g.vx1 = (unsigned)(g.lxf + 1) < (unsigned)tw;
+        g.vy0 = (unsigned)g.lyf < (unsigned)th; g.vy1 = (unsigned)(g.lyf + 1) < (unsigned)th;
+        g.z = rp.q2;
+    }
+    if (!((g.vx0 || g.vx1) && (g.vy0 || g.vy1))) return;
+    const float wsc = fx_weight_scale(logtab, pr.cexp, g.z, pr.clamp_hi);   // 2^90 / dw  (:82-84)
+    const float wx0 = __fmul_rn(g.ax, wsc), wx1 = __fmul_rn(g.bx, wsc);
+    const bool ok[4] = {g.vx0 && g.vy0, g.vx0 && g.vy1, g.vx1 && g.vy0, g.vx1 && g.vy1};   // NW SW NE SE
+    const float w4[4] = {ok[0] ? __fmul_rn(g.ay, wx0) : 0.0f, ok[1] ? __fmul_rn(g.by, wx0) : 0.0f,
+                         ok[2] ? __fmul_rn(g.ay, wx1) : 0.0f, ok[3] ? __fmul_rn(g.by, wx1) : 0.0f};
+    const int o00 = g.lyf * SYN3R_TILE_W + g.lxf, trash = SYN3R_TILE_H * SYN3R_TILE_W + lane;
+    const int oc[4] = {ok[0] ? o00 : trash, ok[1] ? o00 + SYN3R_TILE_W : trash, ok[2] ? o00 + 1 : trash,
+                       ok[3] ? o00 + SYN3R_TILE_W + 1 : trash};
+    unsigned key = 0;
+    if (WINNER) key = zkey_of(g.z);
+    if (SWEEP == 1) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            atomicMax(fx_smem + FX_WMAX * FX_PLANE + oc[c], __float_as_uint(w4[c]));   // positive floats order as ints
+            if (WINNER && w4[c] > 0.0f) atomicMin(fx_smem + FX_ZKEY * FX_PLANE + oc[c], key);
+        }
+    } else {
+        const float c0 = __fmul_rn(px.x, cs_inv), c1 = __fmul_rn(px.y, cs_inv), c2 = __fmul_rn(px.z, cs_inv);
+        unsigned sums = 0;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            unsigned *q4 = fx_smem + oc[c];
+            const unsigned wm = q4[FX_WMAX * FX_PLANE];
+            const float sc = __uint_as_float(((254u + SYN3R_FX_BITS) << 23) - (wm & 0x7f800000u));
+            const float q = __fmul_rn(w4[c], sc);                           // in [0, 2^22)
+            const unsigned vs = (unsigned)(__float_as_int(__fadd_rn(q, SYN3R_FX_MAGIC)) - SYN3R_FX_MAGIC_BITS);
+            const unsigned old = atomicAdd(q4 + FX_S * FX_PLANE, vs);
+            atomicAdd(q4 + FX_I0 * FX_PLANE, (unsigned)(__float_as_int(__fmaf_rn(q, c0, SYN3R_FX_MAGIC)) - SYN3R_FX_MAGIC_BITS));
+            atomicAdd(q4 + FX_I1 * FX_PLANE, (unsigned)(__float_as_int(__fmaf_rn(q, c1, SYN3R_FX_MAGIC)) - SYN3R_FX_MAGIC_BITS));
+            atomicAdd(q4 + FX_I2 * FX_PLANE, (unsigned)(__float_as_int(__fmaf_rn(q, c2, SYN3R_FX_MAGIC)) - SYN3R_FX_MAGIC_BITS));
+            if (WINNER && w4[c] > 0.0f && q4[FX_ZKEY * FX_PLANE] == key) atomicMin(q4 + FX_IDX * FX_PLANE, i);
+            sums |= old + vs;                                               // bit 31 set: a sum passed 2^31
+        }
+        ovf_bits |= sums;
+    }
+}
+
+// One source block (32 x 8 px) of one pair, two rows per iteration (independent projections interleave).
+template <bool WINNER, int SWEEP>
+__device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__restrict__ logtab, const FxPairRegs &pr,
+                                         int p, int s, int bx0, int by0, int tx0, int ty0, int tw, int th, int lane,
+                                         float cs_inv, unsigned &ovf_bits) {
+    const int W = a.g.W, H = a.g.H;
+    const int x = bx0 + lane;
+    const bool live = x < W;
+    const unsigned i0 = (unsigned)s * (unsigned)(H * W) + (unsigned)by0 * W + (live ? x : 0);
+    const double xd = (double)x;
+    const double u0 = __fma_rn(pr.A[0], xd, pr.A[2]), u1 = __fma_rn(pr.A[3], xd, pr.A[5]),
+                 u2 = __fma_rn(pr.A[6], xd, pr.A[8]);
+    const double tx1d = (double)(tx0 - 1), ty1d = (double)(ty0 - 1);
+    const int rows = min(SYN3R_BLK_H, H - by0);                 // >= 1
+    const float4 *src = a.rgbd + i0;
+    const unsigned W2 = 2u * (unsigned)W;
+    // rows r, r+1 of this iteration and (prefetched) of the next; a row index past the block re-reads the last row
+    float4 pxa = ld_stream_f4(src), pxb = ld_stream_f4(src + (rows > 1 ? W : 0));
+    double yd = (double)by0;
+    unsigned ia = i0;
+    int y = by0;
+#pragma unroll 1
+    for (int r = 0; r < rows; r += 2, src += W2, ia += W2, y += 2, yd = __dadd_rn(yd, 2.0)) {
+        const float4 px0 = pxa, px1 = pxb;
+        const bool has1 = r + 1 < rows;
+        pxa = ld_stream_f4(src + (r + 2 < rows ? W2 : 0));
+        pxb = ld_stream_f4(src + (r + 3 < rows ? W2 + W : 0));
+        RowProj p0 = fx_project(pr, u0, u1, u2, yd, (double)px0.w, tx1d, ty1d, tw, th);
+        RowProj p1 = fx_project(pr, u0, u1, u2, __dadd_rn(yd, 1.0), (double)px1.w, tx1d, ty1d, tw, th);
+        if (p0.cand && live)
+            fx_pixel<WINNER, SWEEP>(a, logtab, pr, p0, px0, p, s, x, y, ia, tx0, ty0, tw, th, cs_inv, lane, ovf_bits);
+        __syncwarp();
+        if (p1.cand && live && has1)
+            fx_pixel<WINNER, SWEEP>(a, logtab, pr, p1, px1, p, s, x, y + 1, ia + W, tx0, ty0, tw, th, cs_inv, lane, ovf_bits);
+        __syncwarp();
+    }
+}
+
+__host__ __device__ inline size_t fx_smem_bytes(bool winner) {
+    const size_t cells = (size_t)SYN3R_TILE_W * SYN3R_TILE_H;
+    return (cells + SYN3R_TILE_W) * 4 * (winner ? 7 : 5) + (size_t)SYN3R_LOGTAB * 16 + (SYN3R_LISTA + SYN3R_LISTB) * 4 + 64;
+}
+
+// culls the pair's source blocks against the tile and runs one sweep over the survivors.
+// ctl: [1] nA, [2] nB, [4] / [5] dynamic block counters of sweep 1 / 2, [6] listB is complete and reusable
+template <bool WINNER, int SWEEP>
+__device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, const FxPairRegs &pr, int p, int s,
+                                        int tx0, int ty0, int tx1, int ty1, bool reuse_list, float cs_inv,
+                                        unsigned &ovf_bits) {
+    const TileGeom &g = a.g;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int tw = tx1 - tx0 + 1, th = ty1 - ty0 + 1;
+    int *ctl = sm.ctl;
+    auto run_list = [&](int nB) {
+        for (;;) {
+            int k = 0;
+            if (lane == 0) k = atomicAdd(&ctl[SWEEP == 1 ? 4 : 5], 1);
+            k = __shfl_sync(0xffffffffu, k, 0);
+            if (k >= nB) break;
+            const int org = sm.listB[k];                        // (by0 << 16) | bx0
+            fx_block<WINNER, SWEEP>(a, sm.logtab, pr, p, s, org & 0xffff, org >> 16, tx0, ty0, tw, th, lane, cs_inv,
+                                    ovf_bits);
+        }
+    };
+    if (SWEEP == 2 && reuse_list) {       // the list sweep 1 built is complete: no culling, no barrier
+        run_list(ctl[2]);
+        return;
+    }
+    const CellBox *sbb = a.sb_box + (size_t)p * g.nsb;
+    const CellBox *bbb = a.blk_box + (size_t)p * g.nsb * SYN3R_SB_BLOCKS;
+    for (int base = 0; base < g.nsb; base += SYN3R_LISTA) {
+        __syncthreads();
+        if (tid == 0) ctl[1] = 0;
+        __syncthreads();
+        for (int j = base + tid; j < min(base + SYN3R_LISTA, g.nsb); j += SYN3R_TILE_THREADS)
+            if (box_hits(sbb[j], tx0, ty0, tx1, ty1)) sm.listA[atomicAdd(&ctl[1], 1)] = j;
+        __syncthreads();
+        const int nA = ctl[1];
+        for (int a0 = 0; a0 < nA; a0 += SYN3R_LISTB / SYN3R_SB_BLOCKS) {
+            __syncthreads();
+            if (tid == 0) { ctl[2] = 0; ctl[4] = 0; ctl[5] = 0; }
+            __syncthreads();
+            const int cnt = min(SYN3R_LISTB / SYN3R_SB_BLOCKS, nA - a0) * SYN3R_SB_BLOCKS;
+            for (int j = tid; j < cnt; j += SYN3R_TILE_THREADS) {
+                const int sb = sm.listA[a0 + j / SYN3R_SB_BLOCKS], bi = j % SYN3R_SB_BLOCKS;
+                if (box_hits(bbb[sb * SYN3R_SB_BLOCKS + bi], tx0, ty0, tx1, ty1)) {
+                    int bx0, by0;
+                    block_origin(g, sb, bi, bx0, by0);
+                    sm.listB[atomicAdd(&ctl[2], 1)] = (by0 << 16) | bx0;
+                }
+            }
+            __syncthreads();
+            run_list(ctl[2]);
+        }
+        if (tid == 0 && SWEEP == 1) ctl[6] = (g.nsb <= SYN3R_LISTA && nA <= SYN3R_LISTB / SYN3R_SB_BLOCKS) ? 1 : 0;
+    }
+}
+
+struct CellOut { float v0, v1, v2; bool m, bad; int win; };
+
+// :109-128 for one cell from its integer accumulators
+__device__ __forceinline__ CellOut fx_resolve_cell(unsigned wm, unsigned S, int I0, int I1, int I2, unsigned widx,
+                                                   int flags, float cscale, float gate) {
+    CellOut o;
+    o.m = wm != 0u;                                            // some corner with w > 0 landed here (:112)
+    const float Sf = __uint2float_rn(S);
+    if (flags & SYN3R_FWD_GATE_0P6)                            // sum of weights <= 0.6: undo the per-cell scale
+        o.m = o.m && (__fmul_rn(Sf, __uint_as_float((wm & 0x7f800000u) - ((unsigned)SYN3R_FX_BITS << 23))) <= gate);
+    const float inv = __fdividef(cscale, Sf);
+    o.v0 = o.m ? __fmul_rn(__int2float_rn(I0), inv) : 0.0f;   // :116
+    o.v1 = o.m ? __fmul_rn(__int2float_rn(I1), inv) : 0.0f;
+    o.v2 = o.m ? __fmul_rn(__int2float_rn(I2), inv) : 0.0f;
+    o.bad = (flags & SYN3R_FWD_IS_IMAGE) && (!(o.v0 >= 0.0f) || !(o.v0 <= 256.0f) || !(o.v1 >= 0.0f) ||
+                                             !(o.v1 <= 256.0f) || !(o.v2 >= 0.0f) || !(o.v2 <= 256.0f));   // :121-125
+    o.win = o.m ? (int)widx : -1;
+    return o;
+}
+__device__ __forceinline__ unsigned u8_round(float v) {      // clip + round-half-even (:127-128)
+    return (unsigned)__float2int_rn(fminf(fmaxf(v, 0.0f), 255.0f));
+}
+
+template <bool WINNER>
+__global__ void __launch_bounds__(SYN3R_TILE_THREADS, 1)
+k_fwd_tile_fx(const TileArgs a) {
+    const int CELLS = FX_PLANE, NPL = WINNER ? 7 : 5;          // plane stride incl. the trash row
+    FxAux sm;
+    unsigned char *ptr = reinterpret_cast<unsigned char *>(fx_smem + NPL * CELLS);
+    sm.logtab = reinterpret_cast<double2 *>(ptr); ptr += (size_t)SYN3R_LOGTAB * 16;
+    sm.listA = reinterpret_cast<int *>(ptr); ptr += SYN3R_LISTA * 4;
+    sm.listB = reinterpret_cast<int *>(ptr); ptr += SYN3R_LISTB * 4;
+    sm.ctl = reinterpret_cast<int *>(ptr);
+    int *ctl = sm.ctl;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = SYN3R_TILE_THREADS / 32;
+    const TileGeom g = a.g;
+    const int W = g.W, H = g.H;
+    const unsigned hw = (unsigned)(H * W);
+
+    for (int k = tid; k < SYN3R_LOGTAB; k += SYN3R_TILE_THREADS) {
+        const double c = __hiloint2double(0x3ff00000 + (k << 14) + (1 << 13), 0);    // bin centre
+        sm.logtab[k] = make_double2(__ddiv_rn(1.0, c), log2(c));
+    }
+    for (int k = tid; k < CELLS; k += SYN3R_TILE_THREADS) {
+#pragma unroll
+        for (int pl = 0; pl < 5; ++pl) fx_smem[pl * CELLS + k] = 0u;
+        if (WINNER) { fx_smem[FX_ZKEY * CELLS + k] = ~0u; fx_smem[FX_IDX * CELLS + k] = ~0u; }
+        if (k >= FX_CELLS) fx_smem[FX_WMAX * CELLS + k] = 0x3f800000u;      // trash cells: a finite scale, weights 0
+    }
+    // colour scale: the power of two >= max |colour| over all sources (k_src_stats); exact to divide by
+    const unsigned cb = *a.cmax_bits;
+    const bool colour_bad = cb >= 0x7f000000u;                 // inf / NaN / > 2^127: fp32 path for everything
+    const unsigned ce = min(max((cb >> 23) + ((cb & 0x7fffffu) ? 1u : 0u), 1u), 253u);
+    const float cscale = cb ? __uint_as_float(ce << 23) : 1.0f;
+    const float cs_inv = cb ? __uint_as_float((254u - ce) << 23) : 1.0f;
+    const int n_items = a.n_slots * g.ntiles;
+    const float gate = 0.6f * (float)SYN3R_W_SCALE;
+
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) {
+            ctl[0] = (int)atomicAdd(a.work_counter, 1u);
+            ctl[2] = 0; ctl[3] = 0; ctl[4] = 0; ctl[5] = 0; ctl[6] = 0; ctl[7] = 0;   // empty block list until culled
+        }
+        __syncthreads();
+        const int item = ctl[0];
+        if (item >= n_items) break;
+        if (colour_bad) {
+            if (tid == 0) a.redo_list[atomicAdd(a.redo_count, 1u)] = item;
+            continue;
+        }
+        const int slot = item / g.ntiles, tile = item - slot * g.ntiles;
+        const int tx0 = (tile % g.ntx) * SYN3R_TILE_W, ty0 = (tile / g.ntx) * SYN3R_TILE_H;
+        const int tx1 = min(tx0 + SYN3R_TILE_W, W) - 1, ty1 = min(ty0 + SYN3R_TILE_H, H) - 1;
+        unsigned ovf_bits = 0;
+        auto load_pair = [&](int p, FxPairRegs &pr) -> bool {
+            const PairFast *pf = a.pair_fast + p;
+            pr.cexp = pf->cexp;
+            if (!(pr.cexp < CUDART_INF)) return false;         // max log-depth NaN or 0: every weight is NaN (:84)
+#pragma unroll
+            for (int k = 0; k < 9; ++k) pr.A[k] = pf->A[k];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) pr.b[k] = pf->b[k];
+            pr.k0 = pf->k0; pr.k1 = pf->k1; pr.k2 = pf->k2; pr.k3 = pf->k3; pr.k4 = pf->k4;
+            pr.clamp_hi = pf->pad != 0.0f;
+            return true;
+        };
+        if (!a.pair_slot) {                                    // PAIR mode: the slot's one pair, list built once
+            FxPairRegs pr;
+            const int p = slot, s = a.pair_src[p];
+            if (load_pair(p, pr)) {                            // (a dead pair leaves the tile empty: mask all false)
+                fx_pair<WINNER, 1>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, cs_inv, ovf_bits);
+                __syncthreads();
+                fx_pair<WINNER, 2>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, ctl[6] != 0, cs_inv, ovf_bits);
+            }
+            __syncthreads();
+        } else {                                               // FUSED mode: every pair of the slot, per sweep
+#pragma unroll 1
+            for (int sweep = 1; sweep <= 2; ++sweep) {
+#pragma unroll 1
+                for (int p = 0; p < a.P; ++p) {
+                    if (a.pair_slot[p] != slot) continue;
+                    FxPairRegs pr;
+                    const int s = a.pair_src[p];
+                    if (!load_pair(p, pr)) { ovf_bits = 0x80000000u; continue; }   // NaN weights poison cells: fp32 path
+                    if (sweep == 1) fx_pair<WINNER, 1>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, cs_inv, ovf_bits);
+                    else fx_pair<WINNER, 2>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, cs_inv, ovf_bits);
+                }
+                __syncthreads();
+            }
+        }
+        if (ovf_bits & 0x80000000u) ctl[3] = 1;
+        __syncthreads();
+        const bool redo = ctl[3] != 0;
+        if (redo && tid == 0) a.redo_list[atomicAdd(a.redo_count, 1u)] = item;
+
+        // ---- resolve from shared memory (:109-128) and clear the planes for the next item -----------------
+        bool bad = false;
+        const int tw = tx1 - tx0 + 1, th = ty1 - ty0 + 1;
+        const bool vec = (tw == SYN3R_TILE_W) && ((W & 3) == 0);
+        for (int ly = warp; ly <= SYN3R_TILE_H; ly += nwarps) {          // row TILE_H = the trash row (cleared only)
+            const int c4 = ly * SYN3R_TILE_W + lane * 4;       // this lane's 4 consecutive cells of the row
+            uint4 pl[7];
+#pragma unroll
+            for (int k = 0; k < 7; ++k) {
+                if (k >= NPL) continue;
+                uint4 *pp = reinterpret_cast<uint4 *>(fx_smem + k * CELLS + c4);
+                pl[k] = *pp;
+                const unsigned clr = (k >= FX_ZKEY) ? ~0u : ((k == FX_WMAX && ly == SYN3R_TILE_H) ? 0x3f800000u : 0u);
+                *pp = make_uint4(clr, clr, clr, clr);
+            }
+            if (ly >= th || redo) continue;
+            const unsigned q = (unsigned)slot * hw + (unsigned)(ty0 + ly) * W + tx0 + lane * 4;
+            const unsigned wm[4] = {pl[0].x, pl[0].y, pl[0].z, pl[0].w}, S[4] = {pl[1].x, pl[1].y, pl[1].z, pl[1].w};
+            const unsigned i0[4] = {pl[2].x, pl[2].y, pl[2].z, pl[2].w}, i1[4] = {pl[3].x, pl[3].y, pl[3].z, pl[3].w};
+            const unsigned i2[4] = {pl[4].x, pl[4].y, pl[4].z, pl[4].w};
+            const unsigned wi[4] = {WINNER ? pl[6].x : 0u, WINNER ? pl[6].y : 0u, WINNER ? pl[6].z : 0u, WINNER ? pl[6].w : 0u};
+            CellOut o[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                o[j] = fx_resolve_cell(wm[j], S[j], (int)i0[j], (int)i1[j], (int)i2[j], wi[j], a.flags, cscale, gate);
+                if (vec || lane * 4 + j < tw) bad = bad || o[j].bad;
+            }
+            if (vec) {
+                *reinterpret_cast<unsigned *>(a.out_mask + q) = (unsigned)o[0].m | ((unsigned)o[1].m << 8) |
+                                                                ((unsigned)o[2].m << 16) | ((unsigned)o[3].m << 24);
+                if (a.out_f32) {
+                    float4 *f = reinterpret_cast<float4 *>(a.out_f32 + (size_t)q * 3);
+                    st_stream_f4(f, make_float4(o[0].v0, o[0].v1, o[0].v2, o[1].v0));
+                    st_stream_f4(f + 1, make_float4(o[1].v1, o[1].v2, o[2].v0, o[2].v1));
+                    st_stream_f4(f + 2, make_float4(o[2].v2, o[3].v0, o[3].v1, o[3].v2));
+                }
+                if (a.out_u8) {
+                    unsigned b[12];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { b[3 * j] = u8_round(o[j].v0); b[3 * j + 1] = u8_round(o[j].v1); b[3 * j + 2] = u8_round(o[j].v2); }
+                    unsigned *u = reinterpret_cast<unsigned *>(a.out_u8 + (size_t)q * 3);
+#pragma unroll
+                    for (int k = 0; k < 3; ++k)
+                        st_stream_u32(u + k, b[4 * k] | (b[4 * k + 1] << 8) | (b[4 * k + 2] << 16) | (b[4 * k + 3] << 24));
+                }
+                if (WINNER && a.out_winner)
+                    *reinterpret_cast<int4 *>(a.out_winner + q) = make_int4(o[0].win, o[1].win, o[2].win, o[3].win);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (lane * 4 + j >= tw) continue;
+                    const size_t qq = (size_t)q + j;
+                    a.out_mask[qq] = (uint8_t)o[j].m;
+                    if (a.out_f32) { a.out_f32[3 * qq] = o[j].v0; a.out_f32[3 * qq + 1] = o[j].v1; a.out_f32[3 * qq + 2] = o[j].v2; }
+                    if (a.out_u8) {
+                        a.out_u8[3 * qq] = (uint8_t)u8_round(o[j].v0); a.out_u8[3 * qq + 1] = (uint8_t)u8_round(o[j].v1);
+                        a.out_u8[3 * qq + 2] = (uint8_t)u8_round(o[j].v2);
+                    }
+                    if (WINNER && a.out_winner) a.out_winner[qq] = o[j].win;
+                }
+            }
+        }
+        if (bad) ctl[7] = 1;
+        __syncthreads();
+        if (tid == 0 && ctl[7] && a.out_status) atomicOr(a.out_status + slot, 1);
+    }
+}
+
+}  // namespace syn3r

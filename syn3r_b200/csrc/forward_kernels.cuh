@@ -74,7 +74,7 @@ __device__ __forceinline__ void splat_pixel(const SplatTarget &t, double ox, dou
     if (((xf & xc) < 0) || ((yf & yc) < 0)) return;   // every corner on the ring
     double dw = depth_weight_div(z, Lmax);
     unsigned long long key = 0;
-    if (WINNER) key = ((unsigned long long)ordered_u32(__double2float_rn(z)) << 32) | src_lin;
+    if (WINNER) key = ((unsigned long long)zkey_of(z) << 32) | src_lin;
     // corner order of the reference: NW (fy,fx), SW (cy,fx), NE (fy,cx), SE (cy,cx), :99-107
     const int cxs[4] = {xf, xf, xc, xc}, cys[4] = {yf, yc, yf, yc};
     const double pw[4] = {__dmul_rn(ay, ax), __dmul_rn(by, ax), __dmul_rn(ay, bx), __dmul_rn(by, bx)};

@@ -83,14 +83,16 @@ def forward_pair_params(T_src, T_tgt, K_src, K_tgt, pair_src, pair_tgt):
 
 def forward_warp_batched(rgbd, Kinv_src, pair_par, pair_src, *, pair_slot=None, n_slots=None, depth64=None,
                          src_mask=None, want_f32=True, want_u8=True, want_winner=False, want_flow=False,
-                         gate06=False, is_image=True, out=None, phases=0, exact_weight=False, legacy=False):
+                         gate06=False, is_image=True, out=None, phases=0, exact_weight=False, legacy=False,
+                         fp32_tile=False):
     """Launch the forward warp for P pairs.  All array arguments are CUDA tensors:
     rgbd [S,H,W,4] f32, Kinv_src [S,9] f64, pair_par [P,24] f64, pair_src [P] i32,
     pair_slot [P] i32 or None (PAIR mode).  Returns a dict of CUDA tensors
     (rgb_f32 [n,H,W,3], rgb_u8 [n,H,W,3], mask [n,H,W] u8, winner [n,H,W] i32, flow [P,H,W,2] f64,
     status [n] i32).  `out` may carry preallocated tensors under the same keys.
     `exact_weight`: IEEE log/exp/div for the soft depth weight (default: fast fp64 table path, rel. err < 3e-7);
-    `legacy`: first-generation global-accumulator kernels (A/B measurements)."""
+    `legacy`: first-generation global-accumulator kernels, `fp32_tile`: second-generation per-tile fp32
+    accumulators (A/B measurements; default is the integer block-floating-point tile kernel)."""
     L = nat.lib()
     S, H, W, four = rgbd.shape
     assert four == 4 and rgbd.dtype == torch.float32
@@ -99,7 +101,7 @@ def forward_warp_batched(rgbd, Kinv_src, pair_par, pair_src, *, pair_slot=None, 
     dev = rgbd.device
     flags = (nat.FWD_GATE_0P6 if gate06 else 0) | (nat.FWD_WINNER if want_winner else 0) | \
             (nat.FWD_IS_IMAGE if is_image else 0) | int(phases) | (nat.FWD_EXACT_WEIGHT if exact_weight else 0) | \
-            (nat.FWD_LEGACY_GLOBAL if legacy else 0)
+            (nat.FWD_LEGACY_GLOBAL if legacy else 0) | (nat.FWD_FP32_TILE if fp32_tile else 0)
     o = dict(out or {})
 
     def get(key, want, shape, dtype):
