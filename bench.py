@@ -194,7 +194,7 @@ class ClockSampler:
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from syn3r_b200 import _native as nat, trajectory, warp as w
+    from syn3r_b200 import _native as nat, sharding, trajectory, warp as w
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -289,6 +289,20 @@ def run_ours(args):
                 "dominant_kernel": dominant, "kernel_ms": kern,
                 "kernel_share": {k: v / ksum for k, v in kern.items()}}
 
+    # ---- N > 1: the one exchange step of the path, the gather of finished frames on the diffusion rank -------
+    gather, gather_info = None, None
+    if world > 1:
+        wire = sharding.compact_wire(tw.out_fwd, tw.out_inv)
+        gather = sharding.FrameGather(wire, [tw.P] * world, dst=0)
+        for _ in range(2):
+            gather(wire)
+        ms_g = timed(lambda: gather(wire), max(3, min(args.steps, 10)))
+        tg = torch.tensor([statistics.mean(ms_g)], device=dev, dtype=torch.float64)
+        dist.all_reduce(tg, op=dist.ReduceOp.MAX)
+        nbytes = gather.bytes_received(wire)
+        gather_info = {"ms": float(tg.item()), "bytes_into_rank0": nbytes, "GBps_into_rank0": nbytes / float(tg.item()) / 1e6,
+                       "wire": sorted(wire.keys()), "backend": "nccl grouped send/recv (batch_isend_irecv)"}
+
     # ---- end to end through the plan with HOST buffers ------------------------------------------------
     e2e = None
     if not args.no_e2e:
@@ -296,6 +310,8 @@ def run_ours(args):
             tw.upload(rgbd_h, tgtd_h)
             tw.run()
             tw.download()
+            if gather is not None:
+                gather(wire)
         for _ in range(2):
             step_e2e()
         ms_e = timed(step_e2e, args.steps)
@@ -319,6 +335,8 @@ def run_ours(args):
                 "config": workload_desc(args, S, T, H, W, len(ps)), "clocks": clocks, "e2e": e2e,
                 "gpu_launches": args.steps * tw.launches_per_run(), "roofline": roofline, "cpu_baseline": cpu,
                 "pair_mpix_per_s": world * args.steps * len(ps) * H * W / 1e6 / (total_ms / 1e3)}
+        if gather_info is not None:
+            line["gather"] = gather_info
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -85,6 +85,8 @@ struct FwdWorkspace {
     CellBox *blk_box, *sb_box;
     PairFast *pair_fast;
     int *redo_list;
+    double *blk_zhi;
+    unsigned long long *zlo;
     size_t bytes, acc_bytes, keys_bytes, small_bytes;
 };
 
@@ -105,7 +107,7 @@ static FwdWorkspace fwd_layout(void *base, int H, int W, int S, int n_pairs, int
         return w;
     }
     TileGeom g = make_geom(H, W);
-    w.small_bytes = zb + nb + 256;
+    w.small_bytes = zb + nb + 256 + zb;                 // ... + zlo keys
     size_t stats_b = align_up((size_t)S * g.nsb * SYN3R_SB_BLOCKS * sizeof(BlockStats), 256);
     size_t blk_b = align_up((size_t)n_pairs * g.nsb * SYN3R_SB_BLOCKS * sizeof(CellBox), 256);
     size_t sb_b = align_up((size_t)n_pairs * g.nsb * sizeof(CellBox), 256);
@@ -119,7 +121,10 @@ static FwdWorkspace fwd_layout(void *base, int H, int W, int S, int n_pairs, int
     w.sb_box = (CellBox *)(b + w.small_bytes + stats_b + blk_b);
     w.pair_fast = (PairFast *)(b + w.small_bytes + stats_b + blk_b + sb_b);
     w.redo_list = (int *)(b + w.small_bytes + stats_b + blk_b + sb_b + pf_b);
-    w.bytes = w.small_bytes + stats_b + blk_b + sb_b + pf_b + redo_b;
+    size_t zhi_b = align_up((size_t)n_pairs * g.nsb * SYN3R_SB_BLOCKS * sizeof(double), 256);
+    w.blk_zhi = (double *)(b + w.small_bytes + stats_b + blk_b + sb_b + pf_b + redo_b);
+    w.zlo = (unsigned long long *)(b + zb + nb + 256);
+    w.bytes = w.small_bytes + stats_b + blk_b + sb_b + pf_b + redo_b + zhi_b;
     return w;
 }
 
@@ -268,8 +273,13 @@ int syn3r_forward_warp_batched(const float *rgbd, const double *depth64, const u
         if (phases & SYN3R_FWD_PHASE_ZMAX) {
             SYN3R_TRY_CUDA(cudaMemsetAsync(ws.zmax, 0, ws.small_bytes, st));
             k_src_stats<<<dim3(g.nsb, S), 256, 0, st>>>((const float4 *)rgbd, depth64, g, ws.stats, ws.counter + 16);
+            // boxes + bounds of z' per block, then the exact max z' over the blocks that can hold it
+            k_fwd_prep<<<dim3(g.nsb, P), 32, 0, st>>>((const float4 *)rgbd, depth64, Kinv_src, pair_par, pair_src, g,
+                                                      ws.stats, ws.zmax, ws.znan, ws.blk_box, ws.sb_box, ws.pair_fast,
+                                                      1, ws.blk_zhi, ws.zlo);
             k_fwd_prep<<<dim3(g.nsb, P), 256, 0, st>>>((const float4 *)rgbd, depth64, Kinv_src, pair_par, pair_src, g,
-                                                       ws.stats, ws.zmax, ws.znan, ws.blk_box, ws.sb_box, ws.pair_fast);
+                                                       ws.stats, ws.zmax, ws.znan, ws.blk_box, ws.sb_box, ws.pair_fast,
+                                                       2, ws.blk_zhi, ws.zlo);
             k_fwd_finalize<<<(P + 127) / 128, 128, 0, st>>>(ws.zmax, ws.znan, P, ws.pair_fast);
         }
         if (phases & SYN3R_FWD_PHASE_SPLAT) {

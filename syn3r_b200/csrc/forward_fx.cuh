@@ -246,7 +246,8 @@ __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__res
     const float4 *src = a.rgbd + i0;
     const unsigned W2 = 2u * (unsigned)W;
     // rows r, r+1 of this iteration and (prefetched) of the next; a row index past the block re-reads the last row
-    float4 pxa = ld_stream_f4(src), pxb = ld_stream_f4(src + (rows > 1 ? W : 0));
+    const uint64_t keep = l2_policy_evict_last();
+    float4 pxa = ld_keep_f4(src, keep), pxb = ld_keep_f4(src + (rows > 1 ? W : 0), keep);
     double yd = (double)by0;
     unsigned ia = i0;
     int y = by0;
@@ -254,8 +255,8 @@ __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__res
     for (int r = 0; r < rows; r += 2, src += W2, ia += W2, y += 2, yd = __dadd_rn(yd, 2.0)) {
         const float4 px0 = pxa, px1 = pxb;
         const bool has1 = r + 1 < rows;
-        pxa = ld_stream_f4(src + (r + 2 < rows ? W2 : 0));
-        pxb = ld_stream_f4(src + (r + 3 < rows ? W2 + W : 0));
+        pxa = ld_keep_f4(src + (r + 2 < rows ? W2 : 0), keep);
+        pxb = ld_keep_f4(src + (r + 3 < rows ? W2 + W : 0), keep);
         RowProj p0 = fx_project(pr, u0, u1, u2, yd, (double)px0.w, tx1d, ty1d, tw, th);
         RowProj p1 = fx_project(pr, u0, u1, u2, __dadd_rn(yd, 1.0), (double)px1.w, tx1d, ty1d, tw, th);
         if (p0.cand && live)
@@ -385,6 +386,7 @@ k_fwd_tile_fx(const TileArgs a) {
     const float cs_inv = cb ? __uint_as_float((254u - ce) << 23) : 1.0f;
     const int n_items = a.n_slots * g.ntiles;
     const float gate = 0.6f * (float)SYN3R_W_SCALE;
+    const uint64_t once = l2_policy_evict_first();
 
     for (;;) {
         __syncthreads();
@@ -472,13 +474,13 @@ k_fwd_tile_fx(const TileArgs a) {
                 if (vec || lane * 4 + j < tw) bad = bad || o[j].bad;
             }
             if (vec) {
-                *reinterpret_cast<unsigned *>(a.out_mask + q) = (unsigned)o[0].m | ((unsigned)o[1].m << 8) |
-                                                                ((unsigned)o[2].m << 16) | ((unsigned)o[3].m << 24);
+                st_once_u32(reinterpret_cast<unsigned *>(a.out_mask + q), (unsigned)o[0].m | ((unsigned)o[1].m << 8) |
+                                                                          ((unsigned)o[2].m << 16) | ((unsigned)o[3].m << 24), once);
                 if (a.out_f32) {
                     float4 *f = reinterpret_cast<float4 *>(a.out_f32 + (size_t)q * 3);
-                    st_stream_f4(f, make_float4(o[0].v0, o[0].v1, o[0].v2, o[1].v0));
-                    st_stream_f4(f + 1, make_float4(o[1].v1, o[1].v2, o[2].v0, o[2].v1));
-                    st_stream_f4(f + 2, make_float4(o[2].v2, o[3].v0, o[3].v1, o[3].v2));
+                    st_once_f4(f, make_float4(o[0].v0, o[0].v1, o[0].v2, o[1].v0), once);
+                    st_once_f4(f + 1, make_float4(o[1].v1, o[1].v2, o[2].v0, o[2].v1), once);
+                    st_once_f4(f + 2, make_float4(o[2].v2, o[3].v0, o[3].v1, o[3].v2), once);
                 }
                 if (a.out_u8) {
                     unsigned b[12];
@@ -487,10 +489,10 @@ k_fwd_tile_fx(const TileArgs a) {
                     unsigned *u = reinterpret_cast<unsigned *>(a.out_u8 + (size_t)q * 3);
 #pragma unroll
                     for (int k = 0; k < 3; ++k)
-                        st_stream_u32(u + k, b[4 * k] | (b[4 * k + 1] << 8) | (b[4 * k + 2] << 16) | (b[4 * k + 3] << 24));
+                        st_once_u32(u + k, b[4 * k] | (b[4 * k + 1] << 8) | (b[4 * k + 2] << 16) | (b[4 * k + 3] << 24), once);
                 }
                 if (WINNER && a.out_winner)
-                    *reinterpret_cast<int4 *>(a.out_winner + q) = make_int4(o[0].win, o[1].win, o[2].win, o[3].win);
+                    st_once_i4(reinterpret_cast<int4 *>(a.out_winner + q), make_int4(o[0].win, o[1].win, o[2].win, o[3].win), once);
             } else {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {

@@ -136,9 +136,9 @@ class TrajectoryWarp:
                                  i.get("mask_reproj"), i.get("soft_mask_reproj"), f["status"])
 
     def launches_per_run(self) -> int:
-        """Kernels of libsyn3r_warp.so per run() (memsets not counted): k_src_stats, k_fwd_prep, k_fwd_tile
-        (+ k_reproj_masks)."""
-        return 3 + (1 if self.consistency else 0)
+        """Kernels of libsyn3r_warp.so per run() (memsets not counted): k_src_stats, k_fwd_prep (bounds), k_fwd_prep (pruned max z'),
+        k_fwd_finalize, k_fwd_tile_fx, k_fwd_tile (redo list, normally empty) (+ k_reproj_masks)."""
+        return 6 + (1 if self.consistency else 0)
 
 
 def from_synth(traj, pairs=None, **kw) -> TrajectoryWarp:
