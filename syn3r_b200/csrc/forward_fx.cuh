@@ -51,7 +51,6 @@ struct FxAux {                  // the rest of the shared memory, behind the pla
 struct PixelGeom {              // where a source pixel lands relative to the tile
     int lxf, lyf;               // local cell of the floor corner
     float ax, bx, ay, by;       // proximity factors of the floor / ceil corner per axis (A.1 step 11)
-    bool vx0, vx1, vy0, vy1;    // corner column / row takes part (inside the tile and a distinct cell)
     double z;                   // z' (:174)
 };
 
@@ -81,11 +80,7 @@ __device__ __noinline__ PixelGeom exact_pixel(const double *__restrict__ par_g, 
     axis_cells(oy, yf, yc, g.ay, g.by);
     g.lxf = xf - tx0; g.lyf = yf - ty0;
     // an exact-integer landing puts both "corners" on one cell (N3): the ceil corner is not a distinct cell,
-    // its factor (1.0) joins the floor corner's
-    g.vx0 = (unsigned)g.lxf < (unsigned)tw;
-    g.vy0 = (unsigned)g.lyf < (unsigned)th;
-    g.vx1 = (xc != xf) && (unsigned)(g.lxf + 1) < (unsigned)tw;
-    g.vy1 = (yc != yf) && (unsigned)(g.lyf + 1) < (unsigned)th;
+    // its factor (1.0) joins the floor corner's and its own becomes 0 (a zero weight changes nothing anywhere)
     if (xc == xf) { g.ax = __fadd_rn(g.ax, g.bx); g.bx = 0.0f; }
     if (yc == yf) { g.ay = __fadd_rn(g.ay, g.by); g.by = 0.0f; }
     g.z = z;
@@ -161,52 +156,33 @@ __device__ __forceinline__ RowProj fx_project(const FxPairRegs &pr, double u0, d
     return o;
 }
 
-// Everything after the projection for one candidate pixel; SWEEP 1 = per-cell maxima, SWEEP 2 = accumulation.
-// i = s*H*W + y*W + x (the winner index).  Corners that are not part of the tile are sent, with weight 0, to the
-// lane's own cell of the trash row behind the tile, so the four corners run without a branch.
-template <bool WINNER, int SWEEP>
-__device__ __forceinline__ void fx_pixel(const TileArgs &a, const double2 *__restrict__ logtab, const FxPairRegs &pr,
-                                         const RowProj &rp, const float4 px, int p, int s, int x, int y, unsigned i,
-                                         int tx0, int ty0, int tw, int th, float cs_inv, int lane,
-                                         unsigned &ovf_bits) {
-    const float zf = fabsf(__double2float_rn(rp.q2)), df = fabsf(px.w);
-    const float lhs = __fmul_rn(fminf(fabsf(rp.fx), fabsf(rp.fy)), zf);
-    const float rhs = __fmaf_rn(zf, pr.k2, __fmaf_rn(df, pr.k1, pr.k0));
-    bool slow = !(lhs > rhs);
-    if (WINNER) {
-        // z-key = high word of z': ambiguous when the low word is within 2^14 ulps of a carry, or when the
-        // fast z' is not known to 2^-39 relative
-        slow = slow || ((unsigned)__double2loint(rp.q2) + 16384u < 32768u) ||
-               !(__fmul_rn(zf, 1.8e-12f) > __fmaf_rn(df, pr.k3, pr.k4));
-    }
-    PixelGeom g;
-    if (slow) {
-        g = exact_pixel(a.pair_par + (size_t)p * 24, a.Kinv_src + (size_t)s * 9, x, y, (double)px.w, tx0, ty0, tw, th);
-    } else {
-        const bool negx = rp.fx < 0.0f, negy = rp.fy < 0.0f;
-        g.lxf = rp.nx1 - (negx ? 2 : 1); g.lyf = rp.ny1 - (negy ? 2 : 1);
-        g.ax = negx ? -rp.fx : __fsub_rn(1.0f, rp.fx); g.bx = negx ? __fadd_rn(1.0f, rp.fx) : rp.fx;
-        g.ay = negy ? -rp.fy : __fsub_rn(1.0f, rp.fy); g.by = negy ? __fadd_rn(1.0f, rp.fy) : rp.fy;
-        g.vx0 = (unsigned)g.lxf < (unsigned)tw; g.vx1 = (unsigned)(g.lxf + 1) < (unsigned)tw;
-        g.vy0 = (unsigned)g.lyf < (unsigned)th; g.vy1 = (unsigned)(g.lyf + 1) < (unsigned)th;
-        g.z = rp.q2;
-    }
-    if (!((g.vx0 || g.vx1) && (g.vy0 || g.vy1))) return;
-    const float wsc = fx_weight_scale(logtab, pr.cexp, g.z, pr.clamp_hi);   // 2^90 / dw  (:82-84)
+// Corner updates of one pixel.  LEAN: all four corners are distinct cells inside the tile (the warp voted so):
+// the corner and the plane fold into immediate offsets of one base address, no validity logic.  Otherwise corners
+// that are not part of the tile go, with weight 0, to the lane's own cell of the trash row behind the tile, so
+// that the four corners still run without a branch.
+template <bool WINNER, int SWEEP, bool LEAN>
+__device__ __forceinline__ void fx_corners(const PixelGeom &g, float wsc, const float4 px, unsigned i, float cs_inv,
+                                           int lane, int tw, int th, unsigned &ovf_bits) {
     const float wx0 = __fmul_rn(g.ax, wsc), wx1 = __fmul_rn(g.bx, wsc);
-    const bool ok[4] = {g.vx0 && g.vy0, g.vx0 && g.vy1, g.vx1 && g.vy0, g.vx1 && g.vy1};   // NW SW NE SE
-    const float w4[4] = {ok[0] ? __fmul_rn(g.ay, wx0) : 0.0f, ok[1] ? __fmul_rn(g.by, wx0) : 0.0f,
-                         ok[2] ? __fmul_rn(g.ay, wx1) : 0.0f, ok[3] ? __fmul_rn(g.by, wx1) : 0.0f};
-    const int o00 = g.lyf * SYN3R_TILE_W + g.lxf, trash = SYN3R_TILE_H * SYN3R_TILE_W + lane;
-    const int oc[4] = {ok[0] ? o00 : trash, ok[1] ? o00 + SYN3R_TILE_W : trash, ok[2] ? o00 + 1 : trash,
-                       ok[3] ? o00 + SYN3R_TILE_W + 1 : trash};
+    float w4[4] = {__fmul_rn(g.ay, wx0), __fmul_rn(g.by, wx0), __fmul_rn(g.ay, wx1), __fmul_rn(g.by, wx1)};   // NW SW NE SE
+    const int o00 = g.lyf * SYN3R_TILE_W + g.lxf;
+    int oc[4] = {o00, o00 + SYN3R_TILE_W, o00 + 1, o00 + SYN3R_TILE_W + 1};
+    if (!LEAN) {
+        // (a merged "corner" of an exact-integer landing has weight 0 and is harmless wherever it points)
+        const bool vx0 = (unsigned)g.lxf < (unsigned)tw, vx1 = (unsigned)(g.lxf + 1) < (unsigned)tw;
+        const bool vy0 = (unsigned)g.lyf < (unsigned)th, vy1 = (unsigned)(g.lyf + 1) < (unsigned)th;
+        const bool ok[4] = {vx0 && vy0, vx0 && vy1, vx1 && vy0, vx1 && vy1};
+        const int trash = SYN3R_TILE_H * SYN3R_TILE_W + lane;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) { w4[c] = ok[c] ? w4[c] : 0.0f; oc[c] = ok[c] ? oc[c] : trash; }
+    }
     unsigned key = 0;
     if (WINNER) key = zkey_of(g.z);
     if (SWEEP == 1) {
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             atomicMax(fx_smem + FX_WMAX * FX_PLANE + oc[c], __float_as_uint(w4[c]));   // positive floats order as ints
-            if (WINNER && w4[c] > 0.0f) atomicMin(fx_smem + FX_ZKEY * FX_PLANE + oc[c], key);
+            if (WINNER && (LEAN || w4[c] > 0.0f)) atomicMin(fx_smem + FX_ZKEY * FX_PLANE + oc[c], key);
         }
     } else {
         const float c0 = __fmul_rn(px.x, cs_inv), c1 = __fmul_rn(px.y, cs_inv), c2 = __fmul_rn(px.z, cs_inv);
@@ -222,14 +198,65 @@ __device__ __forceinline__ void fx_pixel(const TileArgs &a, const double2 *__res
             atomicAdd(q4 + FX_I0 * FX_PLANE, (unsigned)(__float_as_int(__fmaf_rn(q, c0, SYN3R_FX_MAGIC)) - SYN3R_FX_MAGIC_BITS));
             atomicAdd(q4 + FX_I1 * FX_PLANE, (unsigned)(__float_as_int(__fmaf_rn(q, c1, SYN3R_FX_MAGIC)) - SYN3R_FX_MAGIC_BITS));
             atomicAdd(q4 + FX_I2 * FX_PLANE, (unsigned)(__float_as_int(__fmaf_rn(q, c2, SYN3R_FX_MAGIC)) - SYN3R_FX_MAGIC_BITS));
-            if (WINNER && w4[c] > 0.0f && q4[FX_ZKEY * FX_PLANE] == key) atomicMin(q4 + FX_IDX * FX_PLANE, i);
+            if (WINNER && (LEAN || w4[c] > 0.0f) && q4[FX_ZKEY * FX_PLANE] == key) atomicMin(q4 + FX_IDX * FX_PLANE, i);
             sums |= old + vs;                                               // bit 31 set: a sum passed 2^31
         }
         ovf_bits |= sums;
     }
 }
 
-// One source block (32 x 8 px) of one pair, two rows per iteration (independent projections interleave).
+// Everything after the projection for the TWO rows a thread owns in one iteration, stage by stage for both rows so
+// that their independent dependency chains interleave.  All 32 lanes stay converged up to the votes.
+// i[j] = s*H*W + y*W + x (the winner index).
+template <bool WINNER, int SWEEP>
+__device__ __forceinline__ void fx_rows2(const TileArgs &a, const double2 *__restrict__ logtab, const FxPairRegs &pr,
+                                         const RowProj (&rp)[2], const float4 (&px)[2], const bool (&cand)[2], int p,
+                                         int s, int x, int y, const unsigned (&i)[2], int tx0, int ty0, int tw, int th,
+                                         float cs_inv, int lane, unsigned &ovf_bits) {
+    if (!__any_sync(0xffffffffu, cand[0] || cand[1])) return;               // nothing of these two rows near the tile
+    PixelGeom g[2];
+    bool any[2], full[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const float zf = fabsf(__double2float_rn(rp[j].q2)), df = fabsf(px[j].w);
+        const float lhs = __fmul_rn(fminf(fabsf(rp[j].fx), fabsf(rp[j].fy)), zf);
+        const float rhs = __fmaf_rn(zf, pr.k2, __fmaf_rn(df, pr.k1, pr.k0));
+        bool slow = !(lhs > rhs);
+        if (WINNER)     // z-key = high word of z': ambiguous when the low word is within 2^14 ulps of a carry, or
+                        // when the fast z' is not known to 2^-39 relative
+            slow = slow || ((unsigned)__double2loint(rp[j].q2) + 16384u < 32768u) ||
+                   !(__fmul_rn(zf, 1.8e-12f) > __fmaf_rn(df, pr.k3, pr.k4));
+        const bool negx = rp[j].fx < 0.0f, negy = rp[j].fy < 0.0f;
+        g[j].lxf = rp[j].nx1 - (negx ? 2 : 1); g[j].lyf = rp[j].ny1 - (negy ? 2 : 1);
+        g[j].ax = negx ? -rp[j].fx : __fsub_rn(1.0f, rp[j].fx); g[j].bx = negx ? __fadd_rn(1.0f, rp[j].fx) : rp[j].fx;
+        g[j].ay = negy ? -rp[j].fy : __fsub_rn(1.0f, rp[j].fy); g[j].by = negy ? __fadd_rn(1.0f, rp[j].fy) : rp[j].fy;
+        g[j].z = rp[j].q2;
+        const bool exact = cand[j] && slow;
+        if (exact)                                                          // rare: the bit-faithful chain decides
+            g[j] = exact_pixel(a.pair_par + (size_t)p * 24, a.Kinv_src + (size_t)s * 9, x, y + j, (double)px[j].w, tx0,
+                               ty0, tw, th);
+        // some corner column AND row inside the tile: lxf in [-1, tw-1], lyf in [-1, th-1]; all four corners
+        // inside (and, not coming from the exact chain, distinct cells with w > 0): lxf in [0, tw-2], lyf in [0, th-2]
+        any[j] = cand[j] && (unsigned)(g[j].lxf + 1) <= (unsigned)tw && (unsigned)(g[j].lyf + 1) <= (unsigned)th;
+        full[j] = cand[j] && !exact && (unsigned)g[j].lxf < (unsigned)(tw - 1) && (unsigned)g[j].lyf < (unsigned)(th - 1);
+    }
+    if (!__any_sync(0xffffffffu, any[0] || any[1])) return;
+    float wsc[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j)                                             // 2^90 / dw  (:82-84); z of an idle row: 1
+        wsc[j] = fx_weight_scale(logtab, pr.cexp, any[j] ? g[j].z : 1.0, pr.clamp_hi);
+    if (__all_sync(0xffffffffu, (full[0] || !any[0]) && (full[1] || !any[1]))) {
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+            if (any[j]) fx_corners<WINNER, SWEEP, true>(g[j], wsc[j], px[j], i[j], cs_inv, lane, tw, th, ovf_bits);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+            if (any[j]) fx_corners<WINNER, SWEEP, false>(g[j], wsc[j], px[j], i[j], cs_inv, lane, tw, th, ovf_bits);
+    }
+}
+
+// One source block (32 x 8 px) of one pair, two rows per iteration.
 template <bool WINNER, int SWEEP>
 __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__restrict__ logtab, const FxPairRegs &pr,
                                          int p, int s, int bx0, int by0, int tx0, int ty0, int tw, int th, int lane,
@@ -245,25 +272,30 @@ __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__res
     const int rows = min(SYN3R_BLK_H, H - by0);                 // >= 1
     const float4 *src = a.rgbd + i0;
     const unsigned W2 = 2u * (unsigned)W;
-    // rows r, r+1 of this iteration and (prefetched) of the next; a row index past the block re-reads the last row
     const uint64_t keep = l2_policy_evict_last();
-    float4 pxa = ld_keep_f4(src, keep), pxb = ld_keep_f4(src + (rows > 1 ? W : 0), keep);
+    // rows r, r+1 of this iteration and (prefetched) of the next; a row index past the block re-reads the last row
+    const unsigned rb = (rows > 1) ? (unsigned)W : 0u;         // offset of the odd row of a pair
+    float4 pxa = ld_keep_f4(src, keep), pxb = ld_keep_f4(src + rb, keep);
     double yd = (double)by0;
     unsigned ia = i0;
     int y = by0;
 #pragma unroll 1
-    for (int r = 0; r < rows; r += 2, src += W2, ia += W2, y += 2, yd = __dadd_rn(yd, 2.0)) {
-        const float4 px0 = pxa, px1 = pxb;
-        const bool has1 = r + 1 < rows;
-        pxa = ld_keep_f4(src + (r + 2 < rows ? W2 : 0), keep);
-        pxb = ld_keep_f4(src + (r + 3 < rows ? W2 + W : 0), keep);
-        RowProj p0 = fx_project(pr, u0, u1, u2, yd, (double)px0.w, tx1d, ty1d, tw, th);
-        RowProj p1 = fx_project(pr, u0, u1, u2, __dadd_rn(yd, 1.0), (double)px1.w, tx1d, ty1d, tw, th);
-        if (p0.cand && live)
-            fx_pixel<WINNER, SWEEP>(a, logtab, pr, p0, px0, p, s, x, y, ia, tx0, ty0, tw, th, cs_inv, lane, ovf_bits);
-        __syncwarp();
-        if (p1.cand && live && has1)
-            fx_pixel<WINNER, SWEEP>(a, logtab, pr, p1, px1, p, s, x, y + 1, ia + W, tx0, ty0, tw, th, cs_inv, lane, ovf_bits);
+    for (int r = 0; r < rows; r += 2, ia += W2, y += 2, yd = __dadd_rn(yd, 2.0)) {
+        const float4 px[2] = {pxa, pxb};
+        if (r + 3 < rows) {                                     // full blocks: always, except the last iteration
+            src += W2;
+            pxa = ld_keep_f4(src, keep);
+            pxb = ld_keep_f4(src + W, keep);
+        } else if (r + 2 < rows) {
+            src += W2;
+            pxa = ld_keep_f4(src, keep);
+            pxb = pxa;
+        }
+        const RowProj rp[2] = {fx_project(pr, u0, u1, u2, yd, (double)px[0].w, tx1d, ty1d, tw, th),
+                               fx_project(pr, u0, u1, u2, __dadd_rn(yd, 1.0), (double)px[1].w, tx1d, ty1d, tw, th)};
+        const bool cand[2] = {rp[0].cand && live, rp[1].cand && live && (r + 1 < rows)};
+        const unsigned i[2] = {ia, ia + (unsigned)W};
+        fx_rows2<WINNER, SWEEP>(a, logtab, pr, rp, px, cand, p, s, x, y, i, tx0, ty0, tw, th, cs_inv, lane, ovf_bits);
         __syncwarp();
     }
 }

@@ -173,7 +173,7 @@ def test_shared_reciprocal_division_is_ieee():
     assert int(cnt.item()) == 0
 
 
-@pytest.mark.parametrize("variant", [{}, {"exact_weight": True}, {"legacy": True}])
+@pytest.mark.parametrize("variant", [{}, {"fp32_tile": True}, {"exact_weight": True}, {"legacy": True}])
 @pytest.mark.parametrize("shape,seed", [((3, 4, 60, 80), 21), ((2, 3, 97, 131), 22), ((1, 2, 16, 8), 23),
                                         ((2, 2, 150, 300), 24)])
 def test_pair_mode_vs_oracle(shape, seed, variant):
