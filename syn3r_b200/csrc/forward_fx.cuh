@@ -256,7 +256,7 @@ __device__ __forceinline__ void fx_rows2(const TileArgs &a, const double2 *__res
     }
 }
 
-// One source block (32 x 8 px) of one pair, two rows per iteration.
+// Half a source block (32 x 4 px from row by0) of one pair, two rows per iteration.
 template <bool WINNER, int SWEEP>
 __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__restrict__ logtab, const FxPairRegs &pr,
                                          int p, int s, int bx0, int by0, int tx0, int ty0, int tw, int th, int lane,
@@ -269,7 +269,8 @@ __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__res
     const double u0 = __fma_rn(pr.A[0], xd, pr.A[2]), u1 = __fma_rn(pr.A[3], xd, pr.A[5]),
                  u2 = __fma_rn(pr.A[6], xd, pr.A[8]);
     const double tx1d = (double)(tx0 - 1), ty1d = (double)(ty0 - 1);
-    const int rows = min(SYN3R_BLK_H, H - by0);                 // >= 1
+    const int rows = min(SYN3R_BLK_H / 2, H - by0);             // this half block's rows inside the image
+    if (rows <= 0) return;
     const float4 *src = a.rgbd + i0;
     const unsigned W2 = 2u * (unsigned)W;
     const uint64_t keep = l2_policy_evict_last();
@@ -320,10 +321,10 @@ __device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, cons
             int k = 0;
             if (lane == 0) k = atomicAdd(&ctl[SWEEP == 1 ? 4 : 5], 1);
             k = __shfl_sync(0xffffffffu, k, 0);
-            if (k >= nB) break;
-            const int org = sm.listB[k];                        // (by0 << 16) | bx0
-            fx_block<WINNER, SWEEP>(a, sm.logtab, pr, p, s, org & 0xffff, org >> 16, tx0, ty0, tw, th, lane, cs_inv,
-                                    ovf_bits);
+            if (k >= 2 * nB) break;                             // work unit = half a block (4 rows): shorter tails
+            const int org = sm.listB[k >> 1];                   // (by0 << 16) | bx0
+            fx_block<WINNER, SWEEP>(a, sm.logtab, pr, p, s, org & 0xffff, (org >> 16) + (k & 1) * (SYN3R_BLK_H / 2), tx0, ty0,
+                                    tw, th, lane, cs_inv, ovf_bits);
         }
     };
     if (SWEEP == 2 && reuse_list) {       // the list sweep 1 built is complete: no culling, no barrier

@@ -135,6 +135,43 @@ class TrajectoryWarp:
         return TrajectoryOutputs(f.get("rgb_f32"), f.get("rgb_u8"), f["mask"], f.get("winner"),
                                  i.get("mask_reproj"), i.get("soft_mask_reproj"), f["status"])
 
+    def _run_range(self, p0: int, p1: int):
+        """Forward warp (+ consistency masks) of pairs [p0, p1) into the matching slices of the outputs."""
+        sl = slice(p0, p1)
+        out_f = {k: (v[sl] if k != "status" else v[sl]) for k, v in self.out_fwd.items()}
+        _w.forward_warp_batched(self.rgbd, self.Kinv_src, self.pair_par[sl], self.pair_src[sl], want_f32=self.want_f32,
+                                want_u8=self.want_u8, want_winner=self.want_winner, is_image=True, out=out_f)
+        if self.consistency:
+            out_i = {k: v[sl] for k, v in self.out_inv.items()}
+            _w.inverse_warp_batched(None, None, self.tgt_depth, self.K_host, self.pair_P[sl], self.pair_src[sl],
+                                    self.pair_tgt[sl], rgbd=self.rgbd, bandwidth=self.bandwidth,
+                                    want=("mask_reproj", "soft_mask_reproj"), out=out_i)
+
+    def step_host(self, rgbd_host: torch.Tensor, tgt_depth_host: Optional[torch.Tensor] = None, chunks: int = 5):
+        """One end-to-end step with HOST buffers: H2D of the inputs, kernels, D2H of every output into the pinned
+        staging buffers.  The pairs are processed in `chunks` contiguous ranges so that the device-to-host copy of
+        one range (on a side stream; PCIe is the bottleneck of this step) overlaps the kernels of the next.
+        Everything is joined back into the current stream before returning; nothing synchronises the host."""
+        assert self.pinned is not None, "construct with pinned_host=True"
+        cur = torch.cuda.current_stream()
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=self.dev)
+        side = self._copy_stream
+        self.upload(rgbd_host, tgt_depth_host)
+        n = max(1, min(int(chunks), self.P))
+        bounds = [(self.P * c) // n for c in range(n + 1)]
+        for c in range(n):
+            p0, p1 = bounds[c], bounds[c + 1]
+            self._run_range(p0, p1)
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            side.wait_event(ev)
+            with torch.cuda.stream(side):
+                for k, v in {**self.out_fwd, **self.out_inv}.items():
+                    self.pinned["out_" + k][p0:p1].copy_(v[p0:p1], non_blocking=True)
+        cur.wait_stream(side)
+        return self.pinned
+
     def launches_per_run(self) -> int:
         """Kernels of libsyn3r_warp.so per run() (memsets not counted): k_src_stats, k_fwd_prep (bounds), k_fwd_prep (pruned max z'),
         k_fwd_finalize, k_fwd_tile_fx, k_fwd_tile (redo list, normally empty) (+ k_reproj_masks)."""

@@ -265,3 +265,24 @@ def test_inverse_vs_oracle_seeded():
                 assert np.array_equal(np.isnan(a), np.isnan(b)) and np.max(np.abs(a[fin] - b[fin]), initial=0) <= 2e-6
             else:
                 assert np.array_equal(a.astype(b.dtype), b, equal_nan=True), (k, p)
+
+
+def test_step_host_matches_run():
+    """The pipelined end-to-end step (H2D, kernels in pair ranges, overlapped D2H) == run() + download()."""
+    from syn3r_b200 import trajectory, warp as w
+    S, T, H, W = 2, 4, 48, 160
+    tr = synth.make_trajectory(S, T, H, W, seed=71)
+    tw = trajectory.from_synth(tr, want_u8=True, pinned_host=True)
+    rgbd_h, tgt_h = torch.from_numpy(w.pack_rgbd(tr.rgb, tr.depth)), torch.from_numpy(tr.depth_tgt)
+    tw.upload(rgbd_h, tgt_h)
+    tw.run()
+    tw.download()
+    torch.cuda.synchronize()
+    ref = {k: v.clone() for k, v in tw.pinned.items() if k.startswith("out_")}
+    for k in ref:
+        tw.pinned[k].zero_()
+    got = tw.step_host(rgbd_h, tgt_h, chunks=3)
+    torch.cuda.synchronize()
+    for k, v in got.items():
+        if k.startswith("out_"):
+            assert torch.equal(torch.nan_to_num(v.float()), torch.nan_to_num(ref[k].float())), k
