@@ -320,25 +320,37 @@ def run_ours(args):
                        "wire": sorted(wire.keys()), "backend": "nccl grouped send/recv (batch_isend_irecv)"}
 
     # ---- end to end through the plan with HOST buffers ------------------------------------------------
-    e2e = None
+    # `e2e`: what the reference's functions hand back to their callers travels to the host — forward_warp's uint8
+    # frame + hole mask (forward_warp.py:182) and the consumed inverse_warp keys mask_reproj + soft_mask_reproj
+    # (diffusionGS.py:1346-1347); the winner index (extension) is computed and stays on the device.
+    # `e2e_all_outputs`: the `value` plan itself with every output (fp32 colour + winner) copied back.
+    e2e, e2e_all = None, None
     if not args.no_e2e:
-        def step_e2e():
-            tw.step_host(rgbd_h, tgtd_h, chunks=args.e2e_chunks)
-            if gather is not None:
-                gather(wire)
-        for _ in range(2):
-            step_e2e()
-        ms_e = timed(step_e2e, args.steps)
-        tot = sum(ms_e)
-        if world > 1:
-            tt = torch.tensor([tot], device=dev, dtype=torch.float64)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            tot = float(tt.item())
-        e2e = {"value": world * args.steps * mpix_step / (tot / 1e3), "unit": UNIT,
-               "h2d_bytes_per_step": tw.h2d_bytes(), "d2h_bytes_per_step": tw.d2h_bytes(),
-               "ms_per_step": tot / args.steps,
-               "how": f"TrajectoryWarp.step_host: pinned H2D of RGB-D + target depth, kernels in {args.e2e_chunks} pair "
-                      "ranges, D2H of every output on a side stream overlapping the next range (PCIe-bound)"}
+        def measure(plan, how):
+            def step_e2e():
+                plan.step_host(rgbd_h, tgtd_h, chunks=args.e2e_chunks)
+                if gather is not None:
+                    gather(wire)
+            for _ in range(2):
+                step_e2e()
+            ms_e = timed(step_e2e, args.steps)
+            tot = sum(ms_e)
+            if world > 1:
+                tt = torch.tensor([tot], device=dev, dtype=torch.float64)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                tot = float(tt.item())
+            return {"value": world * args.steps * mpix_step / (tot / 1e3), "unit": UNIT,
+                    "h2d_bytes_per_step": plan.h2d_bytes(), "d2h_bytes_per_step": plan.d2h_bytes(),
+                    "ms_per_step": tot / args.steps, "host_outputs": list(plan.host_outputs), "how": how}
+        e2e_all = measure(tw, f"TrajectoryWarp.step_host on the `value` plan: pinned H2D of RGB-D + target depth, kernels in "
+                              f"{args.e2e_chunks} pair ranges, D2H of EVERY output (fp32 colour, winner) overlapping the next range")
+        tw_ref = trajectory.from_synth(tr, pairs=(ps, pt), want_f32=False, want_u8=True, want_winner=True, pinned_host=True,
+                                       host_outputs=("rgb_u8", "mask", "mask_reproj", "soft_mask_reproj"))
+        e2e = measure(tw_ref, f"TrajectoryWarp.step_host: pinned H2D of RGB-D + target depth, kernels in {args.e2e_chunks} pair "
+                              "ranges (uint8 frame + hole mask + winner + consistency masks), D2H of the outputs the "
+                              "reference's forward_warp / inverse_warp return to their callers, overlapping the next "
+                              "range (PCIe-bound)")
+        assert int(tw_ref.out_fwd["status"].max().item()) == 0
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -347,8 +359,9 @@ def run_ours(args):
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f64 projection / f32 accumulate", "data": "synthetic",
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64 projection / block-floating-point i32 accumulate / f32 consistency", "data": "synthetic",
                 "config": workload_desc(args, S, T, H, W, len(ps)), "clocks": clocks, "e2e": e2e,
+                "e2e_all_outputs": e2e_all,
                 "gpu_launches": args.steps * tw.launches_per_run(), "roofline": roofline, "cpu_baseline": cpu,
                 "pair_mpix_per_s": world * args.steps * len(ps) * H * W / 1e6 / (total_ms / 1e3)}
         if gather_info is not None:

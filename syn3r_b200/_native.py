@@ -10,7 +10,8 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_lib", "libsyn3r_warp.so")
+# SYN3R_WARP_LIB: a differently configured build of the same library (A/B measurements only)
+LIB_PATH = os.environ.get("SYN3R_WARP_LIB") or os.path.join(_HERE, "_lib", "libsyn3r_warp.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 FWD_GATE_0P6 = 1 << 0

@@ -35,7 +35,8 @@ class TrajectoryWarp:
 
     def __init__(self, S: int, T: int, H: int, W: int, pair_src: Sequence[int], pair_tgt: Sequence[int], *,
                  device=None, consistency: bool = True, want_f32: bool = True, want_u8: bool = False,
-                 want_winner: bool = True, bandwidth: float = 20.0, pinned_host: bool = False):
+                 want_winner: bool = True, bandwidth: float = 20.0, pinned_host: bool = False,
+                 host_outputs: Optional[Sequence[str]] = None):
         self.S, self.T, self.H, self.W = S, T, H, W
         self.pair_src_h = np.asarray(pair_src, np.int32)
         self.pair_tgt_h = np.asarray(pair_tgt, np.int32)
@@ -66,6 +67,13 @@ class TrajectoryWarp:
         if consistency:
             self.out_inv["mask_reproj"] = torch.empty((P, H, W), dtype=torch.uint8, device=d)
             self.out_inv["soft_mask_reproj"] = torch.empty((P, H, W), dtype=torch.float32, device=d)
+        # outputs that travel to the host in step_host()/download(); None = every output.  The reference's own
+        # return values are ("rgb_u8", "mask") from forward_warp (forward_warp.py:182) and the consumed keys
+        # ("mask_reproj", "soft_mask_reproj") of inverse_warp (diffusionGS.py:1346-1347); the rest are extensions
+        # (fp32 colour, winner index) that device-side consumers read in place.
+        allk = list(self.out_fwd) + list(self.out_inv)
+        self.host_outputs = allk if host_outputs is None else [k for k in allk if k in set(host_outputs) | {"status"}]
+        assert host_outputs is None or set(host_outputs) <= set(allk), f"unknown output in {host_outputs}"
         self.pinned = None
         if pinned_host:
             self._alloc_pinned()
@@ -100,8 +108,12 @@ class TrajectoryWarp:
         self.pinned = {"rgbd": pin((S, H, W, 4), torch.float32)}
         if self.consistency:
             self.pinned["tgt_depth"] = pin((T, H, W), torch.float32)
-        for k, v in {**self.out_fwd, **self.out_inv}.items():
+        for k, v in self._host_items():
             self.pinned["out_" + k] = pin(tuple(v.shape), v.dtype)
+
+    def _host_items(self):
+        both = {**self.out_fwd, **self.out_inv}
+        return [(k, both[k]) for k in self.host_outputs]
 
     def upload(self, rgbd_host: torch.Tensor, tgt_depth_host: Optional[torch.Tensor] = None):
         """Async H2D of one step's inputs (pinned host tensors recommended)."""
@@ -113,42 +125,46 @@ class TrajectoryWarp:
         return self.rgbd.numel() * 4 + (self.tgt_depth.numel() * 4 if self.consistency else 0)
 
     def d2h_bytes(self) -> int:
-        return sum(v.numel() * v.element_size() for v in {**self.out_fwd, **self.out_inv}.values())
+        return sum(v.numel() * v.element_size() for _, v in self._host_items())
 
     def download(self):
-        """Async D2H of every output into the pinned staging buffers."""
+        """Async D2H of the host outputs into the pinned staging buffers."""
         assert self.pinned is not None, "construct with pinned_host=True"
-        for k, v in {**self.out_fwd, **self.out_inv}.items():
+        for k, v in self._host_items():
             self.pinned["out_" + k].copy_(v, non_blocking=True)
         return self.pinned
 
     # ---- the hot path --------------------------------------------------------------------------
+    def _forward(self, sl=slice(None), phases=0):
+        out_f = self.out_fwd if sl == slice(None) else {k: v[sl] for k, v in self.out_fwd.items()}
+        _w.forward_warp_batched(self.rgbd, self.Kinv_src, self.pair_par[sl], self.pair_src[sl], want_f32=self.want_f32,
+                                want_u8=self.want_u8, want_winner=self.want_winner, is_image=True, out=out_f,
+                                phases=phases)
+
+    def _inverse(self, sl=slice(None)):
+        out_i = self.out_inv if sl == slice(None) else {k: v[sl] for k, v in self.out_inv.items()}
+        _w.inverse_warp_batched(None, None, self.tgt_depth, self.K_host, self.pair_P[sl], self.pair_src[sl],
+                                self.pair_tgt[sl], rgbd=self.rgbd, bandwidth=self.bandwidth,
+                                want=("mask_reproj", "soft_mask_reproj"), out=out_i)
+
+    def _run_range(self, p0: int, p1: int):
+        """Forward warp (+ consistency masks) of pairs [p0, p1) into the matching slices of the outputs."""
+        sl = slice(None) if (p0 == 0 and p1 == self.P) else slice(p0, p1)
+        if not self.consistency:
+            self._forward(sl)
+        else:
+            self._forward(sl)
+            self._inverse(sl)
+
     def run(self) -> TrajectoryOutputs:
         """Enqueue forward warp (+ consistency masks) for all pairs on the current stream."""
-        _w.forward_warp_batched(self.rgbd, self.Kinv_src, self.pair_par, self.pair_src, want_f32=self.want_f32,
-                                want_u8=self.want_u8, want_winner=self.want_winner, is_image=True, out=self.out_fwd)
-        if self.consistency:
-            _w.inverse_warp_batched(None, None, self.tgt_depth, self.K_host, self.pair_P, self.pair_src,
-                                    self.pair_tgt, rgbd=self.rgbd, bandwidth=self.bandwidth,
-                                    want=("mask_reproj", "soft_mask_reproj"), out=self.out_inv)
+        self._run_range(0, self.P)
         f, i = self.out_fwd, self.out_inv
         return TrajectoryOutputs(f.get("rgb_f32"), f.get("rgb_u8"), f["mask"], f.get("winner"),
                                  i.get("mask_reproj"), i.get("soft_mask_reproj"), f["status"])
 
-    def _run_range(self, p0: int, p1: int):
-        """Forward warp (+ consistency masks) of pairs [p0, p1) into the matching slices of the outputs."""
-        sl = slice(p0, p1)
-        out_f = {k: (v[sl] if k != "status" else v[sl]) for k, v in self.out_fwd.items()}
-        _w.forward_warp_batched(self.rgbd, self.Kinv_src, self.pair_par[sl], self.pair_src[sl], want_f32=self.want_f32,
-                                want_u8=self.want_u8, want_winner=self.want_winner, is_image=True, out=out_f)
-        if self.consistency:
-            out_i = {k: v[sl] for k, v in self.out_inv.items()}
-            _w.inverse_warp_batched(None, None, self.tgt_depth, self.K_host, self.pair_P[sl], self.pair_src[sl],
-                                    self.pair_tgt[sl], rgbd=self.rgbd, bandwidth=self.bandwidth,
-                                    want=("mask_reproj", "soft_mask_reproj"), out=out_i)
-
     def step_host(self, rgbd_host: torch.Tensor, tgt_depth_host: Optional[torch.Tensor] = None, chunks: int = 5):
-        """One end-to-end step with HOST buffers: H2D of the inputs, kernels, D2H of every output into the pinned
+        """One end-to-end step with HOST buffers: H2D of the inputs, kernels, D2H of the host outputs into the pinned
         staging buffers.  The pairs are processed in `chunks` contiguous ranges so that the device-to-host copy of
         one range (on a side stream; PCIe is the bottleneck of this step) overlaps the kernels of the next.
         Everything is joined back into the current stream before returning; nothing synchronises the host."""
@@ -167,7 +183,7 @@ class TrajectoryWarp:
             ev.record(cur)
             side.wait_event(ev)
             with torch.cuda.stream(side):
-                for k, v in {**self.out_fwd, **self.out_inv}.items():
+                for k, v in self._host_items():
                     self.pinned["out_" + k][p0:p1].copy_(v[p0:p1], non_blocking=True)
         cur.wait_stream(side)
         return self.pinned
