@@ -121,11 +121,27 @@ __device__ __forceinline__ float fx_weight_scale(const double2 *__restrict__ log
     return __fmul_rn(e2, __int_as_float((127 + 90 - n) << 23));
 }
 
+// Sweep 1 only needs each cell's power-of-two scale, so its weight may be any UPPER bound of the exact one that is
+// tight to well under a factor of two: 2^(90 - cexp log2(1 + clip(z', 0, 5000))) through lg2.approx / ex2.approx,
+// times (1 + 2^-10).  Error budget of the exponent: cexp * (2^-23 / ln 2 [v in fp32] + 2^-22 [lg2.approx, v < 2])
+// + 72 * (2^-22 [lg2.approx, relative] + 2^-23) <= 2.2e-4 for cexp <= 500, i.e. 1.5e-4 relative on the weight,
+// well inside the 2^-10 pad: w_exact <= w_upper, hence q = w_exact * 2^(21 - exponent(Wmax_upper)) < 2^22 as before,
+// and the cell's largest q is >= 2^21 / (1 + 2^-9).  The hole mask (Wmax != 0) depends on the proximity factors only.
+__device__ __forceinline__ float fx_weight_upper(float cexp_f, float zs) {
+    const float v = __fadd_rn(1.0f, fminf(fmaxf(zs, 0.0f), 5000.0f));
+    float l2, e2;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(v));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e2) : "f"(__fmaf_rn(-cexp_f, l2, 90.0014084f)));   // + log2(1 + 2^-10)
+    return e2;
+}
+
 struct FxPairRegs {             // per-pair values a thread keeps in registers over the pair's blocks
     double A[9], b[3];
     float k0, k1, k2, k3, k4;
     double cexp;
+    float cexp_f;               // cexp in fp32 (relative error 2^-24: 72 * 2^-24 on the exponent, in the budget above)
     bool clamp_hi;
+    bool upper_ok;              // cexp <= 500: sweep 1 may use fx_weight_upper
 };
 
 struct RowProj {                // fast projection of one source pixel, relative to the tile
@@ -198,7 +214,8 @@ __device__ __forceinline__ void fx_corners(const PixelGeom &g, float wsc, const 
             atomicAdd(q4 + FX_I0 * FX_PLANE, (unsigned)(__float_as_int(__fmaf_rn(q, c0, SYN3R_FX_MAGIC)) - SYN3R_FX_MAGIC_BITS));
             atomicAdd(q4 + FX_I1 * FX_PLANE, (unsigned)(__float_as_int(__fmaf_rn(q, c1, SYN3R_FX_MAGIC)) - SYN3R_FX_MAGIC_BITS));
             atomicAdd(q4 + FX_I2 * FX_PLANE, (unsigned)(__float_as_int(__fmaf_rn(q, c2, SYN3R_FX_MAGIC)) - SYN3R_FX_MAGIC_BITS));
-            if (WINNER && (LEAN || w4[c] > 0.0f) && q4[FX_ZKEY * FX_PLANE] == key) atomicMin(q4 + FX_IDX * FX_PLANE, i);
+            if (WINNER)     // branch-free: a corner that does not hold the cell's key offers the neutral element
+                atomicMin(q4 + FX_IDX * FX_PLANE, ((LEAN || w4[c] > 0.0f) && q4[FX_ZKEY * FX_PLANE] == key) ? i : ~0u);
             sums |= old + vs;                                               // bit 31 set: a sum passed 2^31
         }
         ovf_bits |= sums;
@@ -242,9 +259,14 @@ __device__ __forceinline__ void fx_rows2(const TileArgs &a, const double2 *__res
     }
     if (!__any_sync(0xffffffffu, any[0] || any[1])) return;
     float wsc[2];
+    if (SWEEP == 1 && pr.upper_ok) {
 #pragma unroll
-    for (int j = 0; j < 2; ++j)                                             // 2^90 / dw  (:82-84); z of an idle row: 1
-        wsc[j] = fx_weight_scale(logtab, pr.cexp, any[j] ? g[j].z : 1.0, pr.clamp_hi);
+        for (int j = 0; j < 2; ++j) wsc[j] = fx_weight_upper(pr.cexp_f, __double2float_rn(g[j].z));
+    } else {
+#pragma unroll
+        for (int j = 0; j < 2; ++j)                                         // 2^90 / dw  (:82-84); z of an idle row: 1
+            wsc[j] = fx_weight_scale(logtab, pr.cexp, any[j] ? g[j].z : 1.0, pr.clamp_hi);
+    }
     if (__all_sync(0xffffffffu, (full[0] || !any[0]) && (full[1] || !any[1]))) {
 #pragma unroll
         for (int j = 0; j < 2; ++j)
@@ -448,6 +470,8 @@ k_fwd_tile_fx(const TileArgs a) {
             for (int k = 0; k < 3; ++k) pr.b[k] = pf->b[k];
             pr.k0 = pf->k0; pr.k1 = pf->k1; pr.k2 = pf->k2; pr.k3 = pf->k3; pr.k4 = pf->k4;
             pr.clamp_hi = pf->pad != 0.0f;
+            pr.cexp_f = __double2float_rn(pr.cexp);
+            pr.upper_ok = pr.cexp <= 500.0;
             return true;
         };
         if (!a.pair_slot) {                                    // PAIR mode: the slot's one pair, list built once
