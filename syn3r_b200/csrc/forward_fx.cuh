@@ -8,16 +8,19 @@
 // Per work item (output slot, 128x48 target tile), two sweeps over the culled source blocks:
 //   sweep 1   every corner that lands in the tile does  ATOMS.MAX Wmax[cell] <- bits(w)      (w > 0 fp32)
 //             and, for the winner output,               ATOMS.MIN zkey[cell] <- ordered(float z')
+//             and counts itself,                          ATOMS.ADD N[cell] <- 1
 //   sweep 2   the corner's weight is expressed relative to the cell's own power of two,
 //             q = w * 2^(21 - exponent(Wmax[cell])) in (0, 2^22), and accumulated as integers:
-//             S += rint(q), I_c += rint(q * colour_c / cscale)  (4 ATOMS.ADD); the winner index is an
-//             ATOMS.MIN among the corners whose z-key equals the cell's minimum.
+//             S += rint(q), I_c += rint(q * colour_c / cscale)  (4 ATOMS.ADD); rint() is the 1.5 * 2^23
+//             magic-number add, and what is accumulated is the raw bit pattern MAGIC_BITS + rint(.) - the
+//             N * MAGIC_BITS is taken off once per cell in the resolve step (mod 2^32) instead of once per add.
+//             The winner index is an ATOMS.MIN among the corners whose z-key equals the cell's minimum.
 //   resolve   colour = I_c / S * cscale, mask = Wmax > 0, winner; planes are cleared for the next item.
 // A block-floating-point accumulator with a per-cell exponent: the largest contribution of a cell keeps 21-22
 // significant bits, a cell's rounding error is <= N * 2^-22 of full scale for N contributions (typically
 // sqrt(N) * 1e-7), sums are order-independent (bitwise reproducible run to run), and the hole mask does not
-// depend on the accumulation at all.  If a cell's S would pass 2^32 (> 1024 near-maximal contributions) the
-// work item is handed to k_fwd_tile (fp32 CAS accumulation) through a redo list.
+// depend on the accumulation at all.  A cell with N >= 512 contributions could pass S = 2^31 (each q < 2^22): such
+// a work item is handed to k_fwd_tile (fp32 CAS accumulation) through a redo list.
 //
 // The projection is evaluated as q = d (A p) + b with the composite A = K2 R K1inv (12 DFMA + one reciprocal
 // per pixel instead of the reference's ~60-operation chain).  Its floor() can differ from the bit-faithful
@@ -36,10 +39,11 @@ namespace syn3r {
 
 // Shared-memory layout: planes of CELLS 32-bit words, addressed as fx_smem[PLANE * CELLS + cell] so that the
 // plane and the corner offset fold into the immediate field of LDS / ATOMS.
-//   WMAX  fp32 bit pattern of the largest corner weight (0 = untouched)     S   sum of rint(q)
-//   I0..2 sum of rint(q * c / cscale)                                       ZKEY, IDX  winner (WINNER only)
+//   WMAX  fp32 bit pattern of the largest corner weight (0 = untouched)     S   sum of MAGIC_BITS + rint(q)
+//   I0..2 sum of MAGIC_BITS + rint(q * c / cscale)     N  number of corner updates     ZKEY, IDX  winner (WINNER only)
 extern __shared__ __align__(16) unsigned fx_smem[];
-enum { FX_WMAX = 0, FX_S = 1, FX_I0 = 2, FX_I1 = 3, FX_I2 = 4, FX_ZKEY = 5, FX_IDX = 6 };
+enum { FX_WMAX = 0, FX_S = 1, FX_I0 = 2, FX_I1 = 3, FX_I2 = 4, FX_N = 5, FX_ZKEY = 6, FX_IDX = 7 };
+#define FX_MAX_N 512u
 #define FX_CELLS (SYN3R_TILE_W * SYN3R_TILE_H)
 #define FX_PLANE (SYN3R_TILE_W * (SYN3R_TILE_H + 1))       /* one extra row: per-lane trash cells */
 
@@ -178,7 +182,7 @@ __device__ __forceinline__ RowProj fx_project(const FxPairRegs &pr, double u0, d
 // that the four corners still run without a branch.
 template <bool WINNER, int SWEEP, bool LEAN>
 __device__ __forceinline__ void fx_corners(const PixelGeom &g, float wsc, const float4 px, unsigned i, float cs_inv,
-                                           int lane, int tw, int th, unsigned &ovf_bits) {
+                                           int lane, int tw, int th) {
     const float wx0 = __fmul_rn(g.ax, wsc), wx1 = __fmul_rn(g.bx, wsc);
     float w4[4] = {__fmul_rn(g.ay, wx0), __fmul_rn(g.by, wx0), __fmul_rn(g.ay, wx1), __fmul_rn(g.by, wx1)};   // NW SW NE SE
     const int o00 = g.lyf * SYN3R_TILE_W + g.lxf;
@@ -198,27 +202,25 @@ __device__ __forceinline__ void fx_corners(const PixelGeom &g, float wsc, const 
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             atomicMax(fx_smem + FX_WMAX * FX_PLANE + oc[c], __float_as_uint(w4[c]));   // positive floats order as ints
+            atomicAdd(fx_smem + FX_N * FX_PLANE + oc[c], 1u);                          // one per sweep-2 update below
             if (WINNER && (LEAN || w4[c] > 0.0f)) atomicMin(fx_smem + FX_ZKEY * FX_PLANE + oc[c], key);
         }
     } else {
         const float c0 = __fmul_rn(px.x, cs_inv), c1 = __fmul_rn(px.y, cs_inv), c2 = __fmul_rn(px.z, cs_inv);
-        unsigned sums = 0;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             unsigned *q4 = fx_smem + oc[c];
             const unsigned wm = q4[FX_WMAX * FX_PLANE];
             const float sc = __uint_as_float(((254u + SYN3R_FX_BITS) << 23) - (wm & 0x7f800000u));
             const float q = __fmul_rn(w4[c], sc);                           // in [0, 2^22)
-            const unsigned vs = (unsigned)(__float_as_int(__fadd_rn(q, SYN3R_FX_MAGIC)) - SYN3R_FX_MAGIC_BITS);
-            const unsigned old = atomicAdd(q4 + FX_S * FX_PLANE, vs);
-            atomicAdd(q4 + FX_I0 * FX_PLANE, (unsigned)(__float_as_int(__fmaf_rn(q, c0, SYN3R_FX_MAGIC)) - SYN3R_FX_MAGIC_BITS));
-            atomicAdd(q4 + FX_I1 * FX_PLANE, (unsigned)(__float_as_int(__fmaf_rn(q, c1, SYN3R_FX_MAGIC)) - SYN3R_FX_MAGIC_BITS));
-            atomicAdd(q4 + FX_I2 * FX_PLANE, (unsigned)(__float_as_int(__fmaf_rn(q, c2, SYN3R_FX_MAGIC)) - SYN3R_FX_MAGIC_BITS));
+            atomicAdd(q4 + FX_S * FX_PLANE, __float_as_uint(__fadd_rn(q, SYN3R_FX_MAGIC)));
+            atomicAdd(q4 + FX_I0 * FX_PLANE, __float_as_uint(__fmaf_rn(q, c0, SYN3R_FX_MAGIC)));
+            atomicAdd(q4 + FX_I1 * FX_PLANE, __float_as_uint(__fmaf_rn(q, c1, SYN3R_FX_MAGIC)));
+            atomicAdd(q4 + FX_I2 * FX_PLANE, __float_as_uint(__fmaf_rn(q, c2, SYN3R_FX_MAGIC)));
             if (WINNER)     // branch-free: a corner that does not hold the cell's key offers the neutral element
                 atomicMin(q4 + FX_IDX * FX_PLANE, ((LEAN || w4[c] > 0.0f) && q4[FX_ZKEY * FX_PLANE] == key) ? i : ~0u);
-            sums |= old + vs;                                               // bit 31 set: a sum passed 2^31
+            asm volatile("" ::: "memory");          // one corner at a time: keeps the live range of the 16 addends short
         }
-        ovf_bits |= sums;
     }
 }
 
@@ -229,7 +231,7 @@ template <bool WINNER, int SWEEP>
 __device__ __forceinline__ void fx_rows2(const TileArgs &a, const double2 *__restrict__ logtab, const FxPairRegs &pr,
                                          const RowProj (&rp)[2], const float4 (&px)[2], const bool (&cand)[2], int p,
                                          int s, int x, int y, const unsigned (&i)[2], int tx0, int ty0, int tw, int th,
-                                         float cs_inv, int lane, unsigned &ovf_bits) {
+                                         float cs_inv, int lane) {
     if (!__any_sync(0xffffffffu, cand[0] || cand[1])) return;               // nothing of these two rows near the tile
     PixelGeom g[2];
     bool any[2], full[2];
@@ -270,11 +272,11 @@ __device__ __forceinline__ void fx_rows2(const TileArgs &a, const double2 *__res
     if (__all_sync(0xffffffffu, (full[0] || !any[0]) && (full[1] || !any[1]))) {
 #pragma unroll
         for (int j = 0; j < 2; ++j)
-            if (any[j]) fx_corners<WINNER, SWEEP, true>(g[j], wsc[j], px[j], i[j], cs_inv, lane, tw, th, ovf_bits);
+            if (any[j]) fx_corners<WINNER, SWEEP, true>(g[j], wsc[j], px[j], i[j], cs_inv, lane, tw, th);
     } else {
 #pragma unroll
         for (int j = 0; j < 2; ++j)
-            if (any[j]) fx_corners<WINNER, SWEEP, false>(g[j], wsc[j], px[j], i[j], cs_inv, lane, tw, th, ovf_bits);
+            if (any[j]) fx_corners<WINNER, SWEEP, false>(g[j], wsc[j], px[j], i[j], cs_inv, lane, tw, th);
     }
 }
 
@@ -282,7 +284,7 @@ __device__ __forceinline__ void fx_rows2(const TileArgs &a, const double2 *__res
 template <bool WINNER, int SWEEP>
 __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__restrict__ logtab, const FxPairRegs &pr,
                                          int p, int s, int bx0, int by0, int tx0, int ty0, int tw, int th, int lane,
-                                         float cs_inv, unsigned &ovf_bits) {
+                                         float cs_inv) {
     const int W = a.g.W, H = a.g.H;
     const int x = bx0 + lane;
     const bool live = x < W;
@@ -318,22 +320,21 @@ __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__res
                                fx_project(pr, u0, u1, u2, __dadd_rn(yd, 1.0), (double)px[1].w, tx1d, ty1d, tw, th)};
         const bool cand[2] = {rp[0].cand && live, rp[1].cand && live && (r + 1 < rows)};
         const unsigned i[2] = {ia, ia + (unsigned)W};
-        fx_rows2<WINNER, SWEEP>(a, logtab, pr, rp, px, cand, p, s, x, y, i, tx0, ty0, tw, th, cs_inv, lane, ovf_bits);
+        fx_rows2<WINNER, SWEEP>(a, logtab, pr, rp, px, cand, p, s, x, y, i, tx0, ty0, tw, th, cs_inv, lane);
         __syncwarp();
     }
 }
 
 __host__ __device__ inline size_t fx_smem_bytes(bool winner) {
     const size_t cells = (size_t)SYN3R_TILE_W * SYN3R_TILE_H;
-    return (cells + SYN3R_TILE_W) * 4 * (winner ? 7 : 5) + (size_t)SYN3R_LOGTAB * 16 + (SYN3R_LISTA + SYN3R_LISTB) * 4 + 64;
+    return (cells + SYN3R_TILE_W) * 4 * (winner ? 8 : 6) + (size_t)SYN3R_LOGTAB * 16 + (SYN3R_LISTA + SYN3R_LISTB) * 4 + 64;
 }
 
 // culls the pair's source blocks against the tile and runs one sweep over the survivors.
 // ctl: [1] nA, [2] nB, [4] / [5] dynamic block counters of sweep 1 / 2, [6] listB is complete and reusable
 template <bool WINNER, int SWEEP>
 __device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, const FxPairRegs &pr, int p, int s,
-                                        int tx0, int ty0, int tx1, int ty1, bool reuse_list, float cs_inv,
-                                        unsigned &ovf_bits) {
+                                        int tx0, int ty0, int tx1, int ty1, bool reuse_list, float cs_inv) {
     const TileGeom &g = a.g;
     const int tid = threadIdx.x, lane = tid & 31;
     const int tw = tx1 - tx0 + 1, th = ty1 - ty0 + 1;
@@ -346,7 +347,7 @@ __device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, cons
             if (k >= 2 * nB) break;                             // work unit = half a block (4 rows): shorter tails
             const int org = sm.listB[k >> 1];                   // (by0 << 16) | bx0
             fx_block<WINNER, SWEEP>(a, sm.logtab, pr, p, s, org & 0xffff, (org >> 16) + (k & 1) * (SYN3R_BLK_H / 2), tx0, ty0,
-                                    tw, th, lane, cs_inv, ovf_bits);
+                                    tw, th, lane, cs_inv);
         }
     };
     if (SWEEP == 2 && reuse_list) {       // the list sweep 1 built is complete: no culling, no barrier
@@ -409,7 +410,7 @@ __device__ __forceinline__ unsigned u8_round(float v) {      // clip + round-hal
 template <bool WINNER>
 __global__ void __launch_bounds__(SYN3R_TILE_THREADS, 1)
 k_fwd_tile_fx(const TileArgs a) {
-    const int CELLS = FX_PLANE, NPL = WINNER ? 7 : 5;          // plane stride incl. the trash row
+    const int CELLS = FX_PLANE, NPL = WINNER ? 8 : 6;          // plane stride incl. the trash row
     FxAux sm;
     unsigned char *ptr = reinterpret_cast<unsigned char *>(fx_smem + NPL * CELLS);
     sm.logtab = reinterpret_cast<double2 *>(ptr); ptr += (size_t)SYN3R_LOGTAB * 16;
@@ -429,7 +430,7 @@ k_fwd_tile_fx(const TileArgs a) {
     }
     for (int k = tid; k < CELLS; k += SYN3R_TILE_THREADS) {
 #pragma unroll
-        for (int pl = 0; pl < 5; ++pl) fx_smem[pl * CELLS + k] = 0u;
+        for (int pl = 0; pl < FX_ZKEY; ++pl) fx_smem[pl * CELLS + k] = 0u;
         if (WINNER) { fx_smem[FX_ZKEY * CELLS + k] = ~0u; fx_smem[FX_IDX * CELLS + k] = ~0u; }
         if (k >= FX_CELLS) fx_smem[FX_WMAX * CELLS + k] = 0x3f800000u;      // trash cells: a finite scale, weights 0
     }
@@ -459,7 +460,7 @@ k_fwd_tile_fx(const TileArgs a) {
         const int slot = item / g.ntiles, tile = item - slot * g.ntiles;
         const int tx0 = (tile % g.ntx) * SYN3R_TILE_W, ty0 = (tile / g.ntx) * SYN3R_TILE_H;
         const int tx1 = min(tx0 + SYN3R_TILE_W, W) - 1, ty1 = min(ty0 + SYN3R_TILE_H, H) - 1;
-        unsigned ovf_bits = 0;
+        bool poisoned = false;
         auto load_pair = [&](int p, FxPairRegs &pr) -> bool {
             const PairFast *pf = a.pair_fast + p;
             pr.cexp = pf->cexp;
@@ -474,33 +475,45 @@ k_fwd_tile_fx(const TileArgs a) {
             pr.upper_ok = pr.cexp <= 500.0;
             return true;
         };
+        // After sweep 1 the counts are final: a cell with FX_MAX_N or more updates could pass S = 2^31 in sweep 2, so
+        // the item goes to the redo list (the flag is read behind the barrier that ends sweep 2).
+        auto scan_crowded = [&]() {
+            bool crowded = false;
+            for (int k = tid * 4; k < FX_CELLS; k += SYN3R_TILE_THREADS * 4) {
+                const uint4 n = *reinterpret_cast<const uint4 *>(fx_smem + FX_N * CELLS + k);
+                crowded = crowded || max(max(n.x, n.y), max(n.z, n.w)) >= FX_MAX_N;
+            }
+            if (crowded) ctl[3] = 1;
+        };
         if (!a.pair_slot) {                                    // PAIR mode: the slot's one pair, list built once
             FxPairRegs pr;
             const int p = slot, s = a.pair_src[p];
             if (load_pair(p, pr)) {                            // (a dead pair leaves the tile empty: mask all false)
-                fx_pair<WINNER, 1>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, cs_inv, ovf_bits);
+                fx_pair<WINNER, 1>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, cs_inv);
                 __syncthreads();
-                fx_pair<WINNER, 2>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, ctl[6] != 0, cs_inv, ovf_bits);
+                scan_crowded();
+                fx_pair<WINNER, 2>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, ctl[6] != 0, cs_inv);
             }
             __syncthreads();
         } else {                                               // FUSED mode: every pair of the slot, per sweep
 #pragma unroll 1
             for (int sweep = 1; sweep <= 2; ++sweep) {
+                if (sweep == 2) scan_crowded();
 #pragma unroll 1
                 for (int p = 0; p < a.P; ++p) {
                     if (a.pair_slot[p] != slot) continue;
                     FxPairRegs pr;
                     const int s = a.pair_src[p];
-                    if (!load_pair(p, pr)) { ovf_bits = 0x80000000u; continue; }   // NaN weights poison cells: fp32 path
-                    if (sweep == 1) fx_pair<WINNER, 1>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, cs_inv, ovf_bits);
-                    else fx_pair<WINNER, 2>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, cs_inv, ovf_bits);
+                    if (!load_pair(p, pr)) { poisoned = true; continue; }   // NaN weights poison cells: fp32 path
+                    if (sweep == 1) fx_pair<WINNER, 1>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, cs_inv);
+                    else fx_pair<WINNER, 2>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, cs_inv);
                 }
                 __syncthreads();
             }
         }
-        if (ovf_bits & 0x80000000u) ctl[3] = 1;
+        if (poisoned) ctl[3] = 1;
         __syncthreads();
-        const bool redo = ctl[3] != 0;
+        const bool redo = ctl[3] != 0;                         // poisoned or crowded: k_fwd_tile recomputes the item
         if (redo && tid == 0) a.redo_list[atomicAdd(a.redo_count, 1u)] = item;
 
         // ---- resolve from shared memory (:109-128) and clear the planes for the next item -----------------
@@ -509,9 +522,9 @@ k_fwd_tile_fx(const TileArgs a) {
         const bool vec = (tw == SYN3R_TILE_W) && ((W & 3) == 0);
         for (int ly = warp; ly <= SYN3R_TILE_H; ly += nwarps) {          // row TILE_H = the trash row (cleared only)
             const int c4 = ly * SYN3R_TILE_W + lane * 4;       // this lane's 4 consecutive cells of the row
-            uint4 pl[7];
+            uint4 pl[8];
 #pragma unroll
-            for (int k = 0; k < 7; ++k) {
+            for (int k = 0; k < 8; ++k) {
                 if (k >= NPL) continue;
                 uint4 *pp = reinterpret_cast<uint4 *>(fx_smem + k * CELLS + c4);
                 pl[k] = *pp;
@@ -522,12 +535,14 @@ k_fwd_tile_fx(const TileArgs a) {
             const unsigned q = (unsigned)slot * hw + (unsigned)(ty0 + ly) * W + tx0 + lane * 4;
             const unsigned wm[4] = {pl[0].x, pl[0].y, pl[0].z, pl[0].w}, S[4] = {pl[1].x, pl[1].y, pl[1].z, pl[1].w};
             const unsigned i0[4] = {pl[2].x, pl[2].y, pl[2].z, pl[2].w}, i1[4] = {pl[3].x, pl[3].y, pl[3].z, pl[3].w};
-            const unsigned i2[4] = {pl[4].x, pl[4].y, pl[4].z, pl[4].w};
-            const unsigned wi[4] = {WINNER ? pl[6].x : 0u, WINNER ? pl[6].y : 0u, WINNER ? pl[6].z : 0u, WINNER ? pl[6].w : 0u};
+            const unsigned i2[4] = {pl[4].x, pl[4].y, pl[4].z, pl[4].w}, n[4] = {pl[5].x, pl[5].y, pl[5].z, pl[5].w};
+            const unsigned wi[4] = {WINNER ? pl[7].x : 0u, WINNER ? pl[7].y : 0u, WINNER ? pl[7].z : 0u, WINNER ? pl[7].w : 0u};
             CellOut o[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                o[j] = fx_resolve_cell(wm[j], S[j], (int)i0[j], (int)i1[j], (int)i2[j], wi[j], a.flags, cscale, gate);
+                const unsigned off = n[j] * (unsigned)SYN3R_FX_MAGIC_BITS;     // every update added MAGIC_BITS + rint(.)
+                o[j] = fx_resolve_cell(wm[j], S[j] - off, (int)(i0[j] - off), (int)(i1[j] - off), (int)(i2[j] - off), wi[j],
+                                       a.flags, cscale, gate);
                 if (vec || lane * 4 + j < tw) bad = bad || o[j].bad;
             }
             if (vec) {

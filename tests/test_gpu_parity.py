@@ -205,6 +205,21 @@ def test_fused_mode_vs_oracle(variant):
         assert np.array_equal(o["mask"][t].astype(bool), union)
 
 
+def test_crowded_cells_take_redo_path():
+    """A target camera pulled far back: the whole 96x128 source lands on a handful of cells, > 512 corner updates
+    each, which the integer tile kernel hands to the fp32 tile kernel through the redo list (forward_fx.cuh, FX_MAX_N).
+    Neighbouring tiles stay on the integer path; both must agree with the oracle."""
+    tr = synth.make_trajectory(1, 2, 96, 128, seed=51, pose_step=1.0)
+    tr.pose_tgt[0, 2, 3] += 60.0                       # w2c translation along the optical axis: ~30x minification
+    ps, pt = synth.all_pairs(1, 2)
+    o = _run_pairs(tr, ps, pt)
+    for p, (s, t) in enumerate(zip(ps, pt)):
+        r = _oracle_pair(tr, [s], t)
+        if p == 0:
+            assert r["mask"].sum() < 64                # really crowded
+        _check_slot(o, p, r)
+
+
 def test_gate06_and_smooth_rgb():
     tr = synth.make_trajectory(2, 2, 64, 64, seed=41, smooth_rgb=True)
     ps, pt = synth.all_pairs(2, 2)
