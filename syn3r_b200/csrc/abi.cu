@@ -272,7 +272,7 @@ int syn3r_forward_warp_batched(const float *rgbd, const double *depth64, const u
         SYN3R_REQUIRE(P <= 65535 && S <= 65535, "tile path: at most 65535 pairs / sources per call");
         if (phases & SYN3R_FWD_PHASE_ZMAX) {
             SYN3R_TRY_CUDA(cudaMemsetAsync(ws.zmax, 0, ws.small_bytes, st));
-            k_src_stats<<<dim3(g.nsb, S), 256, 0, st>>>((const float4 *)rgbd, depth64, g, ws.stats, ws.counter + 16);
+            k_src_stats<<<dim3(g.nsb, S), 1024, 0, st>>>((const float4 *)rgbd, depth64, g, ws.stats, ws.counter + 16);
             // boxes + bounds of z' per block, then the exact max z' over the blocks that can hold it
             k_fwd_prep<<<dim3(g.nsb, P), 32, 0, st>>>((const float4 *)rgbd, depth64, Kinv_src, pair_par, pair_src, g,
                                                       ws.stats, ws.zmax, ws.znan, ws.blk_box, ws.sb_box, ws.pair_fast,
