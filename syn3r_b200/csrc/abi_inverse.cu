@@ -1,4 +1,5 @@
 // abi_inverse.cu — extern "C" launchers of the backward / consistency path (include/syn3r_warp.h).
+#include <math.h>
 #include <string.h>
 
 #include "inverse_kernels.cuh"
@@ -29,6 +30,19 @@ CamF32 make_cam(const float *K1, const float *K1inv, const float *K2, int H, int
     c.half_w = (float)W / 2.0f;
     c.half_h = (float)H / 2.0f;
     return c;
+}
+
+// smallest float x with sqrt_rn(x) >= bw, so that  sqrt_rn(e2) < bw  <=>  e2 < x  (host sqrtf is correctly rounded).
+// bw NaN -> NaN (nothing passes); bw <= 0 -> 0 (no e2 is below 0); bw = inf -> inf (every finite e2 passes).
+float reproj_threshold_sq(float bw) {
+    if (bw != bw) return bw;
+    if (!(bw > 0.0f)) return 0.0f;
+    if (bw > 3.4e38f) return bw;
+    volatile float x = bw * bw;                        // a few ulps from the answer (inf when bw^2 overflows)
+    if (x > 3.4e38f) x = 3.4028234e38f;
+    while (x > 0.0f && sqrtf(x) >= bw) x = nextafterf(x, 0.0f);
+    while (sqrtf(x) < bw) { if (x >= 3.4028234e38f) return INFINITY; x = nextafterf(x, INFINITY); }
+    return x;
 }
 
 }  // namespace
@@ -76,14 +90,14 @@ int syn3r_inverse_warp_batched(const float *src_img, const float *src_depth, int
         // trajectory hot path: only the consistency-side outputs -> the register-resident specialisation
         SYN3R_REQUIRE(P <= 65535, "lean path: at most 65535 pairs per call");
         dim3 gl((W + SYN3R_RM_COLS - 1) / SYN3R_RM_COLS, (H + SYN3R_RM_ROWS - 1) / SYN3R_RM_ROWS, P);
-        if (src_depth_stride == 4)
-            k_reproj_masks<4><<<gl, SYN3R_RM_COLS, 0, st>>>(cam, pr, src_depth, tgt_depth, H, W, bandwidth,
-                                                            out->mask_reproj, out->soft_mask_reproj, out->reproj_err,
-                                                            out->mask_warp);
-        else
-            k_reproj_masks<1><<<gl, SYN3R_RM_COLS, 0, st>>>(cam, pr, src_depth, tgt_depth, H, W, bandwidth,
-                                                            out->mask_reproj, out->soft_mask_reproj, out->reproj_err,
-                                                            out->mask_warp);
+        const float bw_sq = reproj_threshold_sq(bandwidth), inv_bw = 1.0f / bandwidth;
+#define SYN3R_RM_LAUNCH(DS, ERR)                                                                                     \
+    k_reproj_masks<DS, ERR><<<gl, SYN3R_RM_COLS, 0, st>>>(cam, pr, src_depth, tgt_depth, H, W, bandwidth, bw_sq, inv_bw, \
+                                                          out->mask_reproj, out->soft_mask_reproj, out->reproj_err,   \
+                                                          out->mask_warp)
+        if (src_depth_stride == 4) { if (out->reproj_err) SYN3R_RM_LAUNCH(4, true); else SYN3R_RM_LAUNCH(4, false); }
+        else { if (out->reproj_err) SYN3R_RM_LAUNCH(1, true); else SYN3R_RM_LAUNCH(1, false); }
+#undef SYN3R_RM_LAUNCH
         return check_cuda(cudaGetLastError(), "k_reproj_masks");
     }
     if (need_minmax) {

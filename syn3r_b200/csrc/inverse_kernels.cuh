@@ -219,11 +219,17 @@ __device__ __forceinline__ float tap_ds(const float *__restrict__ img, int H, in
     return ((unsigned)yy < (unsigned)H && (unsigned)xx < (unsigned)W) ? __ldg(img + (size_t)(yy * W + xx) * DS) : 0.0f;
 }
 
-template <int DS>
+// ERR = false (reproj_err not requested, the trajectory case): the error itself is never formed.
+//   mask_reproj   e < bandwidth with e = sqrt_rn(e2)  <=>  e2 < bw_sq, where bw_sq is the smallest float whose
+//                 correctly rounded square root reaches the bandwidth (sqrt_rn is monotone; found on the host by
+//                 reproj_threshold_sq()): the mask stays bit-exact without the IEEE square root;
+//   soft mask     exp(-(e / bw)^3) through sqrt.approx, a reciprocal multiply and ex2.approx: |error| <= 5e-7
+//                 (the bar for this output is 2e-6, it is compared against a host exp() anyway).
+template <int DS, bool ERR>
 __global__ void __launch_bounds__(SYN3R_RM_COLS)
 k_reproj_masks(CamF32 c, InvPairs pr, const float *__restrict__ src_depth, const float *__restrict__ tgt_depth,
-               int H, int W, float bandwidth, uint8_t *__restrict__ o_mask_reproj, float *__restrict__ o_soft,
-               float *__restrict__ o_err, uint8_t *__restrict__ o_mask_warp) {
+               int H, int W, float bandwidth, float bw_sq, float inv_bw, uint8_t *__restrict__ o_mask_reproj,
+               float *__restrict__ o_soft, float *__restrict__ o_err, uint8_t *__restrict__ o_mask_warp) {
     const int p = blockIdx.z, s = pr.pair_src[p], t = pr.pair_tgt[p];
     const int x = blockIdx.x * SYN3R_RM_COLS + threadIdx.x;
     const int y0 = blockIdx.y * SYN3R_RM_ROWS;
@@ -296,14 +302,26 @@ k_reproj_masks(CamF32 c, InvPairs pr, const float *__restrict__ src_depth, const
         const float r0 = dot3_t(c.K1 + 0, B0, B1, B2), r1 = dot3_t(c.K1 + 3, B0, B1, B2),
                     r2 = dot3_t(c.K1 + 6, B0, B1, B2);                                           // :82-83
         const float ex = __fsub_rn(__fdiv_rn(r0, r2), xf), ey = __fsub_rn(__fdiv_rn(r1, r2), yf);
-        const float e = __fsqrt_rn(__fmaf_rn(ey, ey, __fmul_rn(ex, ex)));                        // :86-89
+        const float e2 = __fmaf_rn(ey, ey, __fmul_rn(ex, ex));                                   // :86-89
         const size_t q = (size_t)p * hw + i;
-        if (o_err) o_err[q] = e;
         if (o_mask_warp) o_mask_warp[q] = mw;
-        if (o_mask_reproj) o_mask_reproj[q] = (e < bandwidth) && mw;                             // forward_warp.py:260,267
-        if (o_soft) {
-            const float rr = __fdiv_rn(e, bandwidth);
-            o_soft[q] = expf(-__fmul_rn(__fmul_rn(rr, rr), rr));                                 // :265
+        if (ERR) {
+            const float e = __fsqrt_rn(e2);
+            o_err[q] = e;
+            if (o_mask_reproj) o_mask_reproj[q] = (e < bandwidth) && mw;                         // forward_warp.py:260,267
+            if (o_soft) {
+                const float rr = __fdiv_rn(e, bandwidth);
+                o_soft[q] = expf(-__fmul_rn(__fmul_rn(rr, rr), rr));                             // :265
+            }
+        } else {
+            if (o_mask_reproj) o_mask_reproj[q] = (e2 < bw_sq) && mw;
+            if (o_soft) {
+                float sr, ex2;
+                asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sr) : "f"(e2));
+                const float rr = __fmul_rn(sr, inv_bw);
+                asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(ex2) : "f"(__fmul_rn(__fmul_rn(__fmul_rn(rr, rr), rr), -1.44269504f)));
+                o_soft[q] = ex2;
+            }
         }
     }
 }

@@ -251,8 +251,10 @@ def test_trajectory_plan_matches_per_pair_api(fw):
                              t_(tr.depth_tgt[t][None]), t_(tr.pose_src[s]), t_(tr.pose_tgt[t]),
                              t_(tr.K.astype(np.float32)))
         assert torch.equal(out.mask_reproj[p].bool(), iw["mask_reproj"])
-        assert np.array_equal(out.soft_mask_reproj[p].cpu().numpy(), iw["soft_mask_reproj"].cpu().numpy(),
-                              equal_nan=True)
+        # the trajectory kernel forms the soft mask with sqrt.approx / ex2.approx (inverse_kernels.cuh): <= 2e-6
+        a, b = out.soft_mask_reproj[p].cpu().numpy(), iw["soft_mask_reproj"].cpu().numpy()
+        fin = np.isfinite(a) & np.isfinite(b)
+        assert np.array_equal(np.isnan(a), np.isnan(b)) and np.max(np.abs(a[fin] - b[fin]), initial=0) <= 2e-6
 
 
 def test_inverse_vs_oracle_seeded():
