@@ -284,6 +284,29 @@ def test_inverse_vs_oracle_seeded():
                 assert np.array_equal(a.astype(b.dtype), b, equal_nan=True), (k, p)
 
 
+@pytest.mark.parametrize("bw", [20.0, 10.0, 0.3, 7.77, 1e-3, 1e-30, 0.0, -1.0, float("inf"), 3e19])
+def test_lean_reproj_mask_equals_err_below_bandwidth(bw):
+    """The trajectory kernel never forms sqrt(e2): mask_reproj = e2 < threshold(bw) & mask_warp must equal
+    (sqrt_rn(e2) < bw) & mask_warp of the kernel that does (same launch path, reproj_err requested)."""
+    from syn3r_b200 import warp as w
+    S, T, H, W = 2, 2, 61, 97
+    tr = synth.make_trajectory(S, T, H, W, seed=63, pose_step=2.0)
+    ps, pt = synth.all_pairs(S, T)
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    args = (None, up(tr.depth), up(tr.depth_tgt), tr.K.astype(np.float32),
+            up(w.inverse_pair_params(tr.pose_src, tr.pose_tgt, ps, pt)), up(ps), up(pt))
+    lean = w.inverse_warp_batched(*args, bandwidth=bw, want=("mask_reproj", "soft_mask_reproj", "mask_warp"))
+    full = w.inverse_warp_batched(*args, bandwidth=bw, want=("mask_reproj", "soft_mask_reproj", "mask_warp", "reproj_err"))
+    torch.cuda.synchronize()
+    assert torch.equal(lean["mask_warp"], full["mask_warp"])
+    assert torch.equal(lean["mask_reproj"], full["mask_reproj"])
+    assert torch.equal(full["mask_reproj"].bool(), (full["reproj_err"] < bw) & full["mask_warp"].bool())
+    if 1e-3 <= bw <= 1e3:
+        a, b = lean["soft_mask_reproj"].cpu().numpy(), full["soft_mask_reproj"].cpu().numpy()
+        fin = np.isfinite(a) & np.isfinite(b)
+        assert np.array_equal(np.isnan(a), np.isnan(b)) and np.max(np.abs(a[fin] - b[fin]), initial=0) <= 2e-6
+
+
 def test_step_host_matches_run():
     """The pipelined end-to-end step (H2D, kernels in pair ranges, overlapped D2H) == run() + download()."""
     from syn3r_b200 import trajectory, warp as w
