@@ -257,11 +257,13 @@ k_reproj_masks(CamF32 c, InvPairs pr, const float *__restrict__ src_depth, const
     const float kx0 = __fmul_rn(c.K1inv[0], xf), kx1 = __fmul_rn(c.K1inv[3], xf), kx2 = __fmul_rn(c.K1inv[6], xf);
     const float Wf = (float)W, Hf = (float)H;
     const int rows = min(SYN3R_RM_ROWS, H - y0);
+    float z_next = __ldg(td + (size_t)y0 * W + x);            // one row ahead: the DRAM latency hides behind a row of math
     for (int r = 0; r < rows; ++r) {
         const int y = y0 + r;
         const float yf = (float)y;
         const size_t i = (size_t)y * W + x;
-        const float z = __ldg(td + i);
+        const float z = z_next;
+        if (r + 1 < rows) z_next = __ldg(td + i + W);
         // ---- A.2 steps 3-7: where the target pixel falls in the source view -> mask_warp (:233) -----
         const float c0 = __fmul_rn(xn, z), c1 = __fmul_rn(s_yn[r], z);
         const float Q0 = dot4_t(A + 0, c0, c1, z, 1.0f), Q1 = dot4_t(A + 4, c0, c1, z, 1.0f),
