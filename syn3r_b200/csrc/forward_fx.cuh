@@ -34,6 +34,10 @@
 namespace syn3r {
 
 #define SYN3R_FX_BITS 21
+#ifndef SYN3R_FX_UNIT_ROWS
+#define SYN3R_FX_UNIT_ROWS 4            /* rows of a source block one warp takes at a time (2 per iteration) */
+#endif
+#define SYN3R_FX_UNITS (SYN3R_BLK_H / SYN3R_FX_UNIT_ROWS)
 #define SYN3R_FX_MAGIC 12582912.0f          /* 1.5 * 2^23: low mantissa bits of (v + MAGIC) are rint(v) */
 #define SYN3R_FX_MAGIC_BITS 0x4B400000
 
@@ -293,7 +297,7 @@ __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__res
     const double u0 = __fma_rn(pr.A[0], xd, pr.A[2]), u1 = __fma_rn(pr.A[3], xd, pr.A[5]),
                  u2 = __fma_rn(pr.A[6], xd, pr.A[8]);
     const double tx1d = (double)(tx0 - 1), ty1d = (double)(ty0 - 1);
-    const int rows = min(SYN3R_BLK_H / 2, H - by0);             // this half block's rows inside the image
+    const int rows = min(SYN3R_FX_UNIT_ROWS, H - by0);          // this unit's rows inside the image
     if (rows <= 0) return;
     const float4 *src = a.rgbd + i0;
     const unsigned W2 = 2u * (unsigned)W;
@@ -344,9 +348,9 @@ __device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, cons
             int k = 0;
             if (lane == 0) k = atomicAdd(&ctl[SWEEP == 1 ? 4 : 5], 1);
             k = __shfl_sync(0xffffffffu, k, 0);
-            if (k >= 2 * nB) break;                             // work unit = half a block (4 rows): shorter tails
-            const int org = sm.listB[k >> 1];                   // (by0 << 16) | bx0
-            fx_block<WINNER, SWEEP>(a, sm.logtab, pr, p, s, org & 0xffff, (org >> 16) + (k & 1) * (SYN3R_BLK_H / 2), tx0, ty0,
+            if (k >= SYN3R_FX_UNITS * nB) break;                // work unit = part of a block: shorter tails
+            const int org = sm.listB[k / SYN3R_FX_UNITS];       // (by0 << 16) | bx0
+            fx_block<WINNER, SWEEP>(a, sm.logtab, pr, p, s, org & 0xffff, (org >> 16) + (k % SYN3R_FX_UNITS) * SYN3R_FX_UNIT_ROWS, tx0, ty0,
                                     tw, th, lane, cs_inv);
         }
     };
