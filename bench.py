@@ -41,7 +41,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-sample-seconds", type=float, default=12.0)
-    ap.add_argument("--e2e-chunks", type=int, default=5, help="pair ranges whose D2H overlaps the next range's kernels")
+    ap.add_argument("--e2e-chunks", type=int, default=10, help="pair ranges whose D2H overlaps the next range's kernels")
     return ap.parse_args()
 
 
@@ -211,7 +211,7 @@ def run_ours(args):
 
     S, T, H, W = synth.CONFIGS[args.config]
     tr = synth.make_trajectory(S, T, H, W, seed=rank)        # weak scaling: one trajectory per rank
-    ps, pt = pair_lists(args, S, T)
+    ps, pt = synth.target_major(*pair_lists(args, S, T))    # same pairs; a pair range then needs few target maps
     tw = trajectory.from_synth(tr, pairs=(ps, pt), want_f32=True, want_u8=False, want_winner=True,
                                pinned_host=not args.no_e2e)
     rgbd_h = torch.from_numpy(w.pack_rgbd(tr.rgb, tr.depth))
@@ -327,10 +327,15 @@ def run_ours(args):
     e2e, e2e_all = None, None
     if not args.no_e2e:
         def measure(plan, how):
+            g_wire = g_plan = None
+            if world > 1:                                   # the plan's own wire: uint8 frames for the reference-facing plan
+                g_wire = sharding.compact_wire(plan.out_fwd, plan.out_inv)
+                g_plan = gather if plan is tw else sharding.FrameGather(g_wire, [plan.P] * world, dst=0)
+
             def step_e2e():
                 plan.step_host(rgbd_h, tgtd_h, chunks=args.e2e_chunks)
-                if gather is not None:
-                    gather(wire)
+                if g_plan is not None:
+                    g_plan(g_wire)
             for _ in range(2):
                 step_e2e()
             ms_e = timed(step_e2e, args.steps)
@@ -341,7 +346,8 @@ def run_ours(args):
                 tot = float(tt.item())
             return {"value": world * args.steps * mpix_step / (tot / 1e3), "unit": UNIT,
                     "h2d_bytes_per_step": plan.h2d_bytes(), "d2h_bytes_per_step": plan.d2h_bytes(),
-                    "ms_per_step": tot / args.steps, "host_outputs": list(plan.host_outputs), "how": how}
+                    "ms_per_step": tot / args.steps, "host_outputs": list(plan.host_outputs),
+                    "gather_wire": sorted(g_wire.keys()) if g_wire else None, "how": how}
         e2e_all = measure(tw, f"TrajectoryWarp.step_host on the `value` plan: pinned H2D of RGB-D + target depth, kernels in "
                               f"{args.e2e_chunks} pair ranges, D2H of EVERY output (fp32 colour, winner) overlapping the next range")
         tw_ref = trajectory.from_synth(tr, pairs=(ps, pt), want_f32=False, want_u8=True, want_winner=True, pinned_host=True,

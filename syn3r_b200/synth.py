@@ -115,6 +115,12 @@ def all_pairs(S: int, T: int):
     return ps, pt
 
 
+def target_major(ps, pt):
+    """The same pairs ordered by target first: a pair range then touches few target depth maps (pipelined upload)."""
+    order = np.lexsort((ps, pt))
+    return np.ascontiguousarray(ps[order]), np.ascontiguousarray(pt[order])
+
+
 def reference_policy_pairs(T: int, S: int = 2):
     """The reference's own source policy: target i<12 from the left anchor, else the right one
     (diffusionGS.py:1555-1567)."""

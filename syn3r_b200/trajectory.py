@@ -173,11 +173,22 @@ class TrajectoryWarp:
         if getattr(self, "_copy_stream", None) is None:
             self._copy_stream = torch.cuda.Stream(device=self.dev)
         side = self._copy_stream
-        self.upload(rgbd_host, tgt_depth_host)
+        # inputs: the sources first (every pair needs them); a target's depth map only right before the first pair
+        # range that reads it, so that with target-major pairs the first range starts after S + a few maps, not all
+        self.rgbd.copy_(rgbd_host, non_blocking=True)
+        sent = np.zeros(self.T, bool)
         n = max(1, min(int(chunks), self.P))
         bounds = [(self.P * c) // n for c in range(n + 1)]
         for c in range(n):
             p0, p1 = bounds[c], bounds[c + 1]
+            if self.consistency:
+                need = np.unique(self.pair_tgt_h[p0:p1])
+                need = need[~sent[need]]
+                sent[need] = True
+                # contiguous runs of target indices -> one copy each
+                for run in np.split(need, np.nonzero(np.diff(need) != 1)[0] + 1) if need.size else []:
+                    a, b = int(run[0]), int(run[-1]) + 1
+                    self.tgt_depth[a:b].copy_(tgt_depth_host[a:b], non_blocking=True)
             self._run_range(p0, p1)
             ev = torch.cuda.Event()
             ev.record(cur)
