@@ -1,0 +1,75 @@
+"""CPU restatement of the caller-side post-processing of a warped frame.
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg as the
+checker, never by the product (syn3r_b200/ has no CPU path).
+
+Follows /root/reference/model/diffusionGS.py:1572-1597 (`warp_images`, forward branch) and :1452-1491
+(`warp_images_bw`, backward branch) in plain NumPy, without cv2 / PIL:
+
+  hole      = 1 - mask2, binarised                                   (:1573-1575 / :1453-1455)
+  dilated   = cv2.dilate(hole * 255, ones(5,5))                      (:1578-1579): OR over the 5x5 window centred on
+              the pixel; cv2's default border for a dilation is "ignore what is outside the image"
+  mask_png  = uint8(dilated), three identical channels               (:1580-1581)
+  cond      = float32(uint8(warped * (1 - dilated))) / 255.          (:1586-1590): uint8() truncates toward zero;
+              float32 array / python float stays float32 (one correctly rounded division)
+  latent    = mean over each 8x8 block of dilated (exact in fp64: count / 64), >= 0.2 -> 1 else 0, i.e.
+              count >= 13                                            (:1592-1596)
+  soft      = mean over each 8x8 block of float32(1 - soft_mask_reproj)   (:1484-1487): np.mean of a contiguous
+              float32 run of 64 uses NumPy's unrolled pairwise sum: eight running sums r[j] += a[8 i + j], then
+              ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)), divided by 64; after the reshape/transpose of :1485 element
+              8 i + j of a block is (row i, column j), so r[j] is the column sum, rows in order.
+
+Parity pinned by tests/golden/post_*.npz, which re-execute the reference's statements with cv2 / PIL themselves
+(tests/golden/make_golden_post.py).
+"""
+import numpy as np
+
+
+def dilate5(hole: np.ndarray) -> np.ndarray:
+    """OR over [y-2, y+2] x [x-2, x+2], pixels outside the image ignored.  hole: bool (H, W)."""
+    H, W = hole.shape
+    pad = np.zeros((H + 4, W + 4), bool)
+    pad[2:-2, 2:-2] = hole
+    out = np.zeros((H, W), bool)
+    for dy in range(5):
+        for dx in range(5):
+            out |= pad[dy:dy + H, dx:dx + W]
+    return out
+
+
+def latent_mask(dil: np.ndarray) -> np.ndarray:
+    H, W = dil.shape
+    cnt = dil.reshape(H // 8, 8, W // 8, 8).sum(axis=(1, 3))
+    return (cnt >= 13).astype(np.float64)           # count / 64 >= 0.2
+
+
+def pool_soft(soft: np.ndarray) -> np.ndarray:
+    """8x8 block mean of float32(1 - soft) in NumPy's own summation order (see the module docstring)."""
+    H, W = soft.shape
+    u = (np.float32(1) - soft.astype(np.float32)).reshape(H // 8, 8, W // 8, 8)      # [by, i, bx, j]
+    r = u[:, 0].copy()                                                                  # [by, bx, j]
+    for i in range(1, 8):
+        r = (r + u[:, i]).astype(np.float32)
+    s = ((r[..., 0] + r[..., 1]) + (r[..., 2] + r[..., 3])) + ((r[..., 4] + r[..., 5]) + (r[..., 6] + r[..., 7]))
+    return (s.astype(np.float32) / np.float32(64)).astype(np.float32)
+
+
+def post_forward(warped_u8: np.ndarray, mask2: np.ndarray) -> dict:
+    """diffusionGS.py:1572-1597.  warped_u8 (H,W,3) uint8, mask2 (H,W) bool (True = covered)."""
+    dil = dilate5(~mask2.astype(bool))
+    kept = np.where(dil[..., None], np.uint8(0), warped_u8).astype(np.uint8)
+    return dict(mask_png=np.repeat((dil * np.uint8(255)).astype(np.uint8)[..., None], 3, axis=2),
+                cond=(kept.astype(np.float32) / np.float32(255.0)).astype(np.float32),
+                cond_u8=kept, latent_mask=latent_mask(dil), masks_ero=np.repeat(dil.astype(np.uint8)[..., None], 3, axis=2))
+
+
+def post_backward(warped_f32: np.ndarray, mask2: np.ndarray, soft: np.ndarray) -> dict:
+    """diffusionGS.py:1452-1491.  warped_f32 (H,W,3) float32 in [0, 256), mask2 = mask_reproj, soft (H,W) f32."""
+    dil = dilate5(~mask2.astype(bool))
+    trunc = np.trunc(warped_f32.astype(np.float64)).astype(np.uint8)      # np.uint8(x * 1.0) for x in [0, 256)
+    kept = np.where(dil[..., None], np.uint8(0), trunc).astype(np.uint8)
+    return dict(mask_png=np.repeat((dil * np.uint8(255)).astype(np.uint8)[..., None], 3, axis=2),
+                cond=(kept.astype(np.float32) / np.float32(255.0)).astype(np.float32), cond_u8=kept,
+                cond_ori=(warped_f32 / np.float32(255.0)).astype(np.float32), latent_mask=latent_mask(dil),
+                masks_ero=np.repeat(dil.astype(np.uint8)[..., None], 3, axis=2),
+                soft_ori=(np.float32(1) - soft).astype(np.float32), soft_pooled=pool_soft(soft))

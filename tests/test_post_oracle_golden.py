@@ -1,0 +1,41 @@
+"""CPU: the post-processing oracle (oracle/post_oracle.py) against the golden fixtures that re-executed the
+reference's statements with cv2 / PIL (tests/golden/make_golden_post.py)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle import post_oracle as po  # checker only
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+FW = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "post_fw_*.npz")))
+BW = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "post_bw_*.npz")))
+
+
+def test_fixture_sets_present():
+    assert len(FW) == 6 and len(BW) == 3
+
+
+@pytest.mark.parametrize("name", FW)
+def test_post_forward_oracle_vs_golden(golden, name):
+    g = golden(name)
+    o = po.post_forward(g["in_warped"], g["in_mask2"])
+    for k in ("mask_png", "cond", "latent_mask", "masks_ero"):
+        assert o[k].dtype == g["out_" + k].dtype and np.array_equal(o[k], g["out_" + k]), k
+
+
+@pytest.mark.parametrize("name", BW)
+def test_post_backward_oracle_vs_golden(golden, name):
+    g = golden(name)
+    o = po.post_backward(g["in_warped"], g["in_mask2"], g["in_soft"])
+    for k in ("mask_png", "cond", "cond_ori", "latent_mask", "masks_ero", "soft_ori", "soft_pooled"):
+        assert o[k].dtype == g["out_" + k].dtype and np.array_equal(o[k], g["out_" + k]), k
+
+
+def test_pool_soft_matches_numpy_mean_order():
+    """np.mean over a contiguous float32 run of 64 == the 8-accumulator order restated in pool_soft."""
+    rng = np.random.default_rng(5)
+    s = rng.random((80, 136), dtype=np.float32)
+    u = (1 - s).reshape(10, 8, 17, 8).transpose(0, 2, 1, 3).reshape(10, 17, 64)
+    assert np.array_equal(np.mean(u, axis=2), po.pool_soft(s))
