@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SYN3R_ABI_VERSION 5
+#define SYN3R_ABI_VERSION 6
 
 enum {
     SYN3R_OK = 0,
@@ -166,6 +166,20 @@ int syn3r_consistency_batched(const float *depth1, const float *depth2, const fl
 int syn3r_points_from_depth(const float *depth, const float *Kinv, int H, int W, float *pts, void *stream);
 /* transform_points (consistency.py:25-42): T [16] HOST = pose2 @ inverse(pose1); out = (T [p;1])[:3] / w. */
 int syn3r_transform_points(const float *pts, const float *T, int H, int W, float *out, void *stream);
+
+/* Caller-side post-processing of P warped frames (model/diffusionGS.py:1572-1597 forward branch, :1452-1491 backward
+ * branch), all device pointers, one launch:
+ *   hole = 1 - valid -> cv2.dilate 5x5 (outside ignored) -> out_mask_png [P,H,W] 0/255 (the reference's three
+ *   channels are identical); frame with the dilated holes blanked: out_cond_u8 [P,H,W,3] = uint8(frame * (1 - m))
+ *   and / or out_cond_f32 = that / 255 (float32); out_cond_ori = frame / 255 (:1467); out_latent [P,H/8,W/8] 0/1 =
+ *   (8x8 block mean of the dilated mask >= 0.2); out_soft_pooled [P,H/8,W/8] = 8x8 block mean of 1 - soft in
+ *   NumPy's float32 summation order (:1484-1487).
+ * valid [P,H,W] (mask2 of forward_warp or mask_reproj of inverse_warp; 1 = covered).  The frame is either img_u8
+ * [P,H,W,3] (forward_warp's uint8 frame) or img_chw [P,3,H,W] float32 in [0,256) (inverse_warp's warped_img); the
+ * other is NULL.  soft [P,H,W] or NULL.  Any output may be NULL.  H and W must be multiples of 8. */
+int syn3r_condition_post_batched(const uint8_t *valid, const uint8_t *img_u8, const float *img_chw, const float *soft,
+                                 int P, int H, int W, uint8_t *out_mask_png, uint8_t *out_cond_u8, float *out_cond_f32,
+                                 float *out_cond_ori, uint8_t *out_latent, float *out_soft_pooled, void *stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,92 @@
+"""Caller-side post-processing of warped frames on the device.
+
+The reference does this per frame on the host with cv2 / PIL between `forward_warp` / `inverse_warp` and the SVD
+pipeline (/root/reference/model/diffusionGS.py:1572-1597 `warp_images`, :1452-1491 `warp_images_bw`): hole mask ->
+5x5 dilation -> blanked conditioning frame -> 8x8 block mean thresholded at 0.2 (the latent-resolution mask) and the
+8x8 pooled reprojection uncertainty.  Here it is ONE launch over all frames of a trajectory
+(`syn3r_condition_post_batched`, csrc/postprocess.cuh); there is no CPU path.
+
+  condition_post_batched(...)   device tensors in, device tensors out (what TrajectoryWarp uses)
+  post_forward / post_backward  host arrays in the reference's own shapes and dtypes, for drop-in use and tests
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _native as nat
+
+POST_KEYS = ("mask_png", "cond_u8", "cond_f32", "cond_ori", "latent", "soft_pooled")
+
+
+def condition_post_batched(valid: torch.Tensor, img_u8: Optional[torch.Tensor] = None,
+                           img_chw: Optional[torch.Tensor] = None, soft: Optional[torch.Tensor] = None, *,
+                           want: Sequence[str] = ("mask_png", "cond_u8", "latent"),
+                           out: Optional[Dict[str, torch.Tensor]] = None) -> Dict[str, torch.Tensor]:
+    """valid [P,H,W] u8/bool (1 = covered), img_u8 [P,H,W,3] u8 or img_chw [P,3,H,W] f32, soft [P,H,W] f32: CUDA
+    tensors.  `want` picks from POST_KEYS; returns key -> CUDA tensor (mask_png [P,H,W] u8 0/255, cond_u8 [P,H,W,3],
+    cond_f32 / cond_ori [P,H,W,3] f32, latent [P,H/8,W/8] u8 0/1, soft_pooled [P,H/8,W/8] f32)."""
+    L = nat.lib()
+    assert set(want) <= set(POST_KEYS), f"unknown output in {want}"
+    if valid.dtype == torch.bool:
+        valid = valid.view(torch.uint8)
+    assert valid.dtype == torch.uint8 and valid.dim() == 3
+    P, H, W = valid.shape
+    assert H % 8 == 0 and W % 8 == 0, "H and W must be multiples of 8 (diffusionGS.py:1593 reshapes to 8x8 blocks)"
+    dev = valid.device
+    if img_u8 is not None:
+        assert img_u8.shape == (P, H, W, 3) and img_u8.dtype == torch.uint8
+    if img_chw is not None:
+        assert img_chw.shape == (P, 3, H, W) and img_chw.dtype == torch.float32
+    if soft is not None:
+        assert soft.shape == (P, H, W) and soft.dtype == torch.float32
+    shapes = {"mask_png": ((P, H, W), torch.uint8), "cond_u8": ((P, H, W, 3), torch.uint8),
+              "cond_f32": ((P, H, W, 3), torch.float32), "cond_ori": ((P, H, W, 3), torch.float32),
+              "latent": ((P, H // 8, W // 8), torch.uint8), "soft_pooled": ((P, H // 8, W // 8), torch.float32)}
+    o = dict(out or {})
+    for k in want:
+        shp, dt = shapes[k]
+        t = o.get(k)
+        if t is None:
+            t = o[k] = torch.empty(shp, dtype=dt, device=dev)
+        assert t.shape == torch.Size(shp) and t.dtype == dt and t.is_contiguous()
+    ptr = lambda k: nat.ptr(o[k]) if k in want else None  # noqa: E731
+    nat.check(L.syn3r_condition_post_batched(nat.ptr(valid), nat.ptr(img_u8), nat.ptr(img_chw), nat.ptr(soft), P, H, W,
+                                             ptr("mask_png"), ptr("cond_u8"), ptr("cond_f32"), ptr("cond_ori"),
+                                             ptr("latent"), ptr("soft_pooled"),
+                                             torch.cuda.current_stream(dev).cuda_stream),
+              "syn3r_condition_post_batched")
+    return {k: o[k] for k in want}
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        raise nat.Syn3rNativeError("syn3r_b200.conditioning needs a CUDA device; there is no CPU path")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def post_forward(warped_frame2: np.ndarray, mask2: np.ndarray) -> dict:
+    """The block of diffusionGS.py:1572-1597 for ONE frame, host arrays in and out, reference dtypes:
+    mask_png (H,W,3) uint8, cond (H,W,3) float32, latent_mask (H/8,W/8) float64."""
+    d = _dev()
+    o = condition_post_batched(torch.from_numpy(np.ascontiguousarray(mask2)).to(d)[None],
+                               img_u8=torch.from_numpy(np.ascontiguousarray(warped_frame2, dtype=np.uint8)).to(d)[None],
+                               want=("mask_png", "cond_f32", "latent"))
+    return dict(mask_png=np.repeat(o["mask_png"][0].cpu().numpy()[..., None], 3, axis=2),
+                cond=o["cond_f32"][0].cpu().numpy(), latent_mask=o["latent"][0].cpu().numpy().astype(np.float64))
+
+
+def post_backward(warped_frame2: np.ndarray, mask2: np.ndarray, soft_mask_reproj: np.ndarray) -> dict:
+    """The block of diffusionGS.py:1452-1491 for ONE frame: warped_frame2 (H,W,3) float32 (warped_img transposed to
+    HWC as at :1444), mask2 = mask_reproj (H,W) bool, soft_mask_reproj (H,W) float32."""
+    d = _dev()
+    chw = torch.from_numpy(np.ascontiguousarray(np.moveaxis(np.asarray(warped_frame2, np.float32), -1, 0))).to(d)[None]
+    o = condition_post_batched(torch.from_numpy(np.ascontiguousarray(mask2)).to(d)[None], img_chw=chw,
+                               soft=torch.from_numpy(np.ascontiguousarray(soft_mask_reproj, dtype=np.float32)).to(d)[None],
+                               want=("mask_png", "cond_f32", "cond_ori", "latent", "soft_pooled"))
+    return dict(mask_png=np.repeat(o["mask_png"][0].cpu().numpy()[..., None], 3, axis=2),
+                cond=o["cond_f32"][0].cpu().numpy(), cond_ori=o["cond_ori"][0].cpu().numpy(),
+                latent_mask=o["latent"][0].cpu().numpy().astype(np.float64),
+                soft_pooled=o["soft_pooled"][0].cpu().numpy())

@@ -1,0 +1,27 @@
+// abi_post.cu — extern "C" launcher of the warped-frame post-processing (include/syn3r_warp.h).
+#include "postprocess.cuh"
+
+using namespace syn3r;
+
+extern "C" {
+
+int syn3r_condition_post_batched(const uint8_t *valid, const uint8_t *img_u8, const float *img_chw, const float *soft,
+                                 int P, int H, int W, uint8_t *out_mask_png, uint8_t *out_cond_u8, float *out_cond_f32,
+                                 float *out_cond_ori, uint8_t *out_latent, float *out_soft_pooled, void *stream) {
+    SYN3R_REQUIRE(valid != nullptr, "the valid mask is required");
+    SYN3R_REQUIRE(P >= 0 && H > 0 && W > 0, "bad sizes");
+    // the reference reshapes to (H/8, 8, W/8, 8) (diffusionGS.py:1593): sizes that do not divide raise there too
+    SYN3R_REQUIRE(H % 8 == 0 && W % 8 == 0, "H and W must be multiples of 8 (latent grid of 8x8 blocks)");
+    SYN3R_REQUIRE(!(img_u8 && img_chw), "give the frame either as uint8 HWC or as float32 CHW, not both");
+    SYN3R_REQUIRE(!(out_cond_u8 || out_cond_f32 || out_cond_ori) || img_u8 || img_chw, "frame outputs need a frame input");
+    SYN3R_REQUIRE(!out_soft_pooled || soft, "soft_pooled needs the soft mask");
+    SYN3R_REQUIRE(P <= 65535, "at most 65535 frames per call");
+    if (P == 0) return SYN3R_OK;
+    PostArgs a{valid, img_u8, img_chw, soft, H, W, out_mask_png, out_cond_u8, out_cond_f32, out_cond_ori, out_latent,
+               out_soft_pooled};
+    dim3 grid((W + SYN3R_PP_TW - 1) / SYN3R_PP_TW, (H + SYN3R_PP_TH - 1) / SYN3R_PP_TH, P);
+    k_condition_post<<<grid, SYN3R_PP_TW, 0, (cudaStream_t)stream>>>(a);
+    return check_cuda(cudaGetLastError(), "k_condition_post");
+}
+
+}  // extern "C"

@@ -1,0 +1,85 @@
+"""GPU parity of the warped-frame post-processing through the C ABI: against the golden
+fixtures (reference statements re-executed with cv2 / PIL) and against the NumPy oracle at full size."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import post_oracle as po  # noqa: E402  (checker only)
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+FW = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "post_fw_*.npz")))
+BW = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "post_bw_*.npz")))
+
+
+@pytest.mark.parametrize("name", FW)
+def test_post_forward_golden(golden, name):
+    from syn3r_b200 import conditioning as c
+    g = golden(name)
+    o = c.post_forward(g["in_warped"], g["in_mask2"])
+    for k in ("mask_png", "cond", "latent_mask"):
+        assert o[k].dtype == g["out_" + k].dtype and np.array_equal(o[k], g["out_" + k]), k
+
+
+@pytest.mark.parametrize("name", BW)
+def test_post_backward_golden(golden, name):
+    from syn3r_b200 import conditioning as c
+    g = golden(name)
+    o = c.post_backward(g["in_warped"], g["in_mask2"], g["in_soft"])
+    for k in ("mask_png", "cond", "cond_ori", "latent_mask", "soft_pooled"):
+        assert o[k].dtype == g["out_" + k].dtype and np.array_equal(o[k], g["out_" + k]), k
+
+
+def test_post_batched_full_size_vs_oracle():
+    """5 frames at 576x1024 (the reference's own 72x128 latent grid), ragged hole structure, every output."""
+    from syn3r_b200 import conditioning as c
+    rng = np.random.default_rng(77)
+    P, H, W = 5, 576, 1024
+    valid = rng.random((P, H, W)) > 0.003
+    valid[0, 100:160, 300:420] = False
+    valid[1, :, :3] = False
+    valid[2] = True
+    valid[3] = False
+    img = rng.integers(0, 256, (P, H, W, 3), dtype=np.uint8)
+    soft = np.exp(-(rng.random((P, H, W), dtype=np.float32) * 3) ** 3).astype(np.float32)
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    o = c.condition_post_batched(up(valid), img_u8=up(img), soft=up(soft), want=c.POST_KEYS)
+    torch.cuda.synchronize()
+    for p in range(P):
+        r = po.post_forward(img[p], valid[p])
+        assert np.array_equal(o["mask_png"][p].cpu().numpy(), r["mask_png"][..., 0]), p
+        assert np.array_equal(o["cond_u8"][p].cpu().numpy(), r["cond_u8"]), p
+        assert np.array_equal(o["cond_f32"][p].cpu().numpy(), r["cond"]), p
+        assert np.array_equal(o["cond_ori"][p].cpu().numpy(), img[p].astype(np.float32) / np.float32(255)), p
+        assert np.array_equal(o["latent"][p].cpu().numpy().astype(np.float64), r["latent_mask"]), p
+        assert np.array_equal(o["soft_pooled"][p].cpu().numpy(), po.pool_soft(soft[p])), p
+    # properties: dilation only grows holes; an all-covered frame passes through; an all-hole frame is blank
+    assert bool((o["mask_png"].cpu().numpy() >= np.where(valid, 0, 255)).all())
+    assert np.array_equal(o["cond_u8"][2].cpu().numpy(), img[2]) and int(o["latent"][2].sum()) == 0
+    assert int(o["cond_u8"][3].max()) == 0 and int(o["latent"][3].min()) == 1
+
+
+def test_post_rejects_sizes_that_do_not_divide_by_8():
+    from syn3r_b200 import conditioning as c
+    with pytest.raises(AssertionError):
+        c.condition_post_batched(torch.ones((1, 20, 24), dtype=torch.uint8, device="cuda"))
+
+
+def test_post_float_frame_truncates_like_np_uint8():
+    """backward branch: np.uint8(float32 frame * (1 - m)) truncates toward zero (diffusionGS.py:1468)."""
+    from syn3r_b200 import conditioning as c
+    rng = np.random.default_rng(3)
+    H, W = 32, 48
+    f = (rng.random((H, W, 3), dtype=np.float32) * np.float32(255.9)).astype(np.float32)
+    f[0, 0] = [0.0, 254.99998, 255.5]
+    m = np.ones((H, W), bool)
+    m[10:12, 20:23] = False
+    s = rng.random((H, W), dtype=np.float32)
+    o = c.post_backward(f, m, s)
+    r = po.post_backward(f, m, s)
+    for k in ("mask_png", "cond", "cond_ori", "latent_mask", "soft_pooled"):
+        assert np.array_equal(o[k], r[k]), k
