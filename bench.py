@@ -305,6 +305,31 @@ def run_ours(args):
                 "note": "instruction-issue bound, not HBM bound: see DESIGN.md 'Roofline' (fp64 projection + "
                         "soft-z weight + 16 integer shared-memory atomics per pair-pixel)"}
 
+    # ---- the callers' per-frame post-processing as one launch per branch (HBM-bound byte work) ----
+    post = None
+    if H % 8 == 0 and W % 8 == 0:
+        from syn3r_b200 import conditioning
+        P_ = len(ps)
+        m_fw, m_bw = tw.out_fwd["mask"], tw.out_inv["mask_reproj"]
+        img8 = torch.randint(0, 256, (P_, H, W, 3), dtype=torch.uint8, device=dev)
+        o_fw, o_bw = {}, {}
+
+        def post_fw():
+            o_fw.update(conditioning.condition_post_batched(m_fw, img_u8=img8, want=("mask_png", "cond_u8", "latent"), out=o_fw))
+
+        def post_bw():
+            o_bw.update(conditioning.condition_post_batched(m_bw, soft=tw.out_inv["soft_mask_reproj"],
+                                                            want=("latent", "soft_pooled"), out=o_bw))
+        post_fw(); post_bw()
+        t_fw = statistics.mean(timed(post_fw, n_k, between=flush.zero_))
+        t_bw = statistics.mean(timed(post_bw, n_k, between=flush.zero_))
+        b_fw = P_ * hw * 8 + P_ * (hw // 64)                  # valid 1 + frame 3 in; png 1 + blanked frame 3 + latent out
+        b_bw = P_ * hw * 5 + P_ * (hw // 64) * 5              # valid 1 + soft 4 in; latent 1 + pooled 4 per 8x8 block out
+        post = {"kernel": "k_condition_post", "forward_branch_ms": t_fw, "backward_branch_ms": t_bw,
+                "forward_branch": {"algorithmic_bytes": b_fw, "achieved_GBps": b_fw / t_fw / 1e6, "frac": b_fw / t_fw / 1e6 / peak},
+                "backward_branch": {"algorithmic_bytes": b_bw, "achieved_GBps": b_bw / t_bw / 1e6, "frac": b_bw / t_bw / 1e6 / peak},
+                "scope": "diffusionGS.py:1572-1597 / :1452-1491 for all pairs; not part of `value` (SURVEY 8f rank 1)"}
+
     # ---- N > 1: the one exchange step of the path, the gather of finished frames on the diffusion rank -------
     gather, gather_info = None, None
     if world > 1:
@@ -372,6 +397,8 @@ def run_ours(args):
                 "pair_mpix_per_s": world * args.steps * len(ps) * H * W / 1e6 / (total_ms / 1e3)}
         if gather_info is not None:
             line["gather"] = gather_info
+        if post is not None:
+            line["post"] = post
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

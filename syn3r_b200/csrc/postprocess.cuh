@@ -5,8 +5,10 @@
 // at 0.2 (= 13 of 64 pixels), 8x8 block mean of 1 - soft_mask_reproj in NumPy's own summation order.
 //
 // HBM-bound byte work: one CTA owns a 256 x 16 pixel tile of one frame (32 x 2 latent cells); the valid mask is
-// staged in shared memory with its 2-pixel halo, dilated separably (5-wide OR along x, then along y), and every
-// input and output byte is touched once.  Algorithmic bytes per pixel: valid 1 + image 3 (uint8) or 12 (fp32) in;
+// staged in shared memory with its 2-pixel halo (32-bit loads), dilated separably (5-wide OR along x, then along y)
+// into a byte plane, and every input and output byte is touched once with 8- or 16-byte accesses: the uint8 frame
+// as a flat run of 768 bytes per tile row (byte b belongs to pixel b / 3), the mask png 8 pixels at a time, the
+// soft mask as float4 (a thread owns 4 of a block's 8 columns, its lane partner the other 4).  Algorithmic bytes per pixel: valid 1 + image 3 (uint8) or 12 (fp32) in;
 // mask png 1, blanked frame 3 (uint8) and / or 12 (fp32), soft 4 in; 1/64 + 4/64 for the latent outputs.
 #pragma once
 #include "common.cuh"
@@ -30,93 +32,171 @@ struct PostArgs {
     float *soft_pooled;        // [P,H/8,W/8] or null
 };
 
+__device__ __forceinline__ float u8_over_255(unsigned v) { return __fdiv_rn((float)v, 255.0f); }      // :1590
+
 __global__ void __launch_bounds__(SYN3R_PP_TW)
 k_condition_post(const PostArgs a) {
-    __shared__ uint8_t s_hole[SYN3R_PP_TH + 4][SYN3R_PP_TW + 8];
-    __shared__ uint8_t s_hor[SYN3R_PP_TH + 4][SYN3R_PP_TW];
+    // four pixels per 32-bit word, one byte (0 / 1) each
+    __shared__ uint32_t s_hole_w[SYN3R_PP_TH + 4][SYN3R_PP_TW / 4 + 4];     // columns x0 - 4 .. x0 + 259
+    __shared__ uint32_t s_hor_w[SYN3R_PP_TH + 4][SYN3R_PP_TW / 4];
+    __shared__ __align__(16) uint32_t s_dil_w[SYN3R_PP_TH][SYN3R_PP_TW / 4];
+    uint8_t (*s_dil)[SYN3R_PP_TW] = reinterpret_cast<uint8_t (*)[SYN3R_PP_TW]>(s_dil_w);
     const int t = threadIdx.x, p = blockIdx.z;
     const int x0 = blockIdx.x * SYN3R_PP_TW, y0 = blockIdx.y * SYN3R_PP_TH;
     const int H = a.H, W = a.W;
     const size_t hw = (size_t)H * W;
+    const int tw = min(SYN3R_PP_TW, W - x0), th = min(SYN3R_PP_TH, H - y0);        // multiples of 8
     const uint8_t *valid = a.valid + (size_t)p * hw;
 
-    // ---- stage hole = !valid with a 2-pixel halo; outside the image there is no hole (cv2.dilate ignores it) ----
-    for (int r = 0; r < SYN3R_PP_TH + 4; ++r) {
-        const int gy = y0 - 2 + r;
-        for (int c = t; c < SYN3R_PP_TW + 4; c += SYN3R_PP_TW) {
-            const int gx = x0 - 2 + c;
-            uint8_t h = 0;
-            if ((unsigned)gy < (unsigned)H && (unsigned)gx < (unsigned)W) h = valid[(size_t)gy * W + gx] == 0;
-            s_hole[r][c] = h;
+    // ---- stage hole = !valid with its halo; outside the image there is no hole (cv2.dilate ignores it) ----------
+    constexpr int WPR = SYN3R_PP_TW / 4 + 2;                // words per staged row: x0 - 4 .. x0 + 259
+    for (int idx = t; idx < (SYN3R_PP_TH + 4) * WPR; idx += SYN3R_PP_TW) {
+        const int r = idx / WPR, w = idx - r * WPR;
+        const int gy = y0 - 2 + r, gx = x0 - 4 + 4 * w;
+        uint32_t v = 0x01010101u;                           // covered
+        if ((unsigned)gy < (unsigned)H && (unsigned)gx < (unsigned)W)
+            v = __ldg(reinterpret_cast<const uint32_t *>(valid + (size_t)gy * W + gx));
+        s_hole_w[r][w] = __vcmpeq4(v, 0u) & 0x01010101u;
+    }
+    __syncthreads();
+    // separable 5x5 OR on the packed words: the neighbours at -2 .. +2 are funnel shifts over the adjacent words
+    constexpr int WT = SYN3R_PP_TW / 4;
+    for (int idx = t; idx < (SYN3R_PP_TH + 4) * WT; idx += SYN3R_PP_TW) {
+        const int r = idx / WT, j = idx - r * WT;
+        const uint32_t prev = s_hole_w[r][j], cur = s_hole_w[r][j + 1], next = s_hole_w[r][j + 2];
+        s_hor_w[r][j] = cur | __funnelshift_r(cur, next, 8) | __funnelshift_r(cur, next, 16) |
+                        __funnelshift_l(prev, cur, 8) | __funnelshift_l(prev, cur, 16);
+    }
+    __syncthreads();
+    for (int idx = t; idx < SYN3R_PP_TH * WT; idx += SYN3R_PP_TW) {
+        const int r = idx / WT, j = idx - r * WT;
+        s_dil_w[r][j] = s_hor_w[r][j] | s_hor_w[r + 1][j] | s_hor_w[r + 2][j] | s_hor_w[r + 3][j] | s_hor_w[r + 4][j];
+    }
+    __syncthreads();
+
+    // ---- mask png: 8 pixels per access (:1580-1581) -------------------------------------------------------------------
+    if (a.mask_png)
+        for (int u = t; u < SYN3R_PP_TH * (SYN3R_PP_TW / 8); u += SYN3R_PP_TW) {
+            const int r = u / (SYN3R_PP_TW / 8), c = (u % (SYN3R_PP_TW / 8)) * 8;
+            if (r < th && c < tw) {
+                uint2 d = *reinterpret_cast<const uint2 *>(&s_dil[r][c]);
+                d.x *= 255u; d.y *= 255u;                   // bytes 0 / 1 -> 0 / 255, no carries between bytes
+                *reinterpret_cast<uint2 *>(a.mask_png + (size_t)p * hw + (size_t)(y0 + r) * W + x0 + c) = d;
+            }
         }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int r = 0; r < SYN3R_PP_TH + 4; ++r)
-        s_hor[r][t] = s_hole[r][t] | s_hole[r][t + 1] | s_hole[r][t + 2] | s_hole[r][t + 3] | s_hole[r][t + 4];
-    __syncthreads();
 
-    const int gx = x0 + t;
-    const bool col_in = gx < W;
-    unsigned dil = 0;                                       // bit r: pixel (y0 + r, gx) is inside a dilated hole
+    // ---- the frame, blanked inside the dilated holes (:1586-1590) --------------------------------------------------------
+    if (a.img_u8) {
+        // a tile row is a flat run of 3 tw bytes; a unit = 8 pixels = 24 bytes = three 8-byte accesses, and the byte
+        // mask of the unit is six byte permutations of the eight dilation bytes (byte b belongs to pixel b / 3)
+        for (int u = t; u < SYN3R_PP_TH * (SYN3R_PP_TW / 8); u += SYN3R_PP_TW) {
+            const int r = u / (SYN3R_PP_TW / 8), c = (u % (SYN3R_PP_TW / 8)) * 8;
+            if (r >= th || c >= tw) continue;
+            const size_t base = ((size_t)p * hw + (size_t)(y0 + r) * W + x0 + c) * 3;
+            const uint2 *src = reinterpret_cast<const uint2 *>(a.img_u8 + base);
+            const uint2 i0 = __ldg(src), i1 = __ldg(src + 1), i2 = __ldg(src + 2);
+            uint2 d = *reinterpret_cast<const uint2 *>(&s_dil[r][c]);
+            d.x *= 255u; d.y *= 255u;                       // 0xff where the pixel is blanked
+            const uint32_t in[6] = {i0.x, i0.y, i1.x, i1.y, i2.x, i2.y};
+            const uint32_t m[6] = {__byte_perm(d.x, 0u, 0x1000), __byte_perm(d.x, 0u, 0x2211), __byte_perm(d.x, 0u, 0x3332),
+                                   __byte_perm(d.y, 0u, 0x1000), __byte_perm(d.y, 0u, 0x2211), __byte_perm(d.y, 0u, 0x3332)};
+            uint32_t o[6];
 #pragma unroll
-    for (int r = 0; r < SYN3R_PP_TH; ++r) {
-        const unsigned d = s_hor[r][t] | s_hor[r + 1][t] | s_hor[r + 2][t] | s_hor[r + 3][t] | s_hor[r + 4][t];
-        dil |= (d ? 1u : 0u) << r;
-    }
-
-    // ---- per-pixel outputs ------------------------------------------------------------------------------------------
-    for (int r = 0; r < SYN3R_PP_TH; ++r) {
-        const int gy = y0 + r;
-        if (gy >= H || !col_in) break;
-        const size_t i = (size_t)gy * W + gx, q = (size_t)p * hw + i;
-        const bool d = (dil >> r) & 1u;
-        if (a.mask_png) a.mask_png[q] = d ? 255 : 0;                                          // :1580-1581
-        if (a.img_u8 || a.img_chw) {
-            unsigned c[3];
-            float f[3] = {0.f, 0.f, 0.f};
+            for (int k = 0; k < 6; ++k) o[k] = in[k] & ~m[k];
+            if (a.cond_u8) {
+                uint2 *dst = reinterpret_cast<uint2 *>(a.cond_u8 + base);
+                dst[0] = make_uint2(o[0], o[1]); dst[1] = make_uint2(o[2], o[3]); dst[2] = make_uint2(o[4], o[5]);
+            }
+            if (a.cond_f32) {
+                float4 *dst = reinterpret_cast<float4 *>(a.cond_f32 + base);
 #pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                if (a.img_u8) {
-                    c[k] = a.img_u8[q * 3 + k];
-                } else {
-                    f[k] = a.img_chw[((size_t)p * 3 + k) * hw + i];
-                    c[k] = (unsigned)__float2int_rz(f[k]) & 0xffu;                          // np.uint8(.): truncation
+                for (int k = 0; k < 6; ++k)
+                    dst[k] = make_float4(u8_over_255(o[k] & 0xffu), u8_over_255((o[k] >> 8) & 0xffu),
+                                         u8_over_255((o[k] >> 16) & 0xffu), u8_over_255(o[k] >> 24));
+            }
+            if (a.cond_ori) {                               // frame / 255 (:1467)
+                float4 *dst = reinterpret_cast<float4 *>(a.cond_ori + base);
+#pragma unroll
+                for (int k = 0; k < 6; ++k)
+                    dst[k] = make_float4(u8_over_255(in[k] & 0xffu), u8_over_255((in[k] >> 8) & 0xffu),
+                                         u8_over_255((in[k] >> 16) & 0xffu), u8_over_255(in[k] >> 24));
+            }
+        }
+    } else if (a.img_chw) {
+        // float32 planes (inverse_warp's warped_img): 4 pixels per thread and row, np.uint8() truncation (:1468)
+        for (int u = t; u < SYN3R_PP_TH * (SYN3R_PP_TW / 4); u += SYN3R_PP_TW) {
+            const int r = u / (SYN3R_PP_TW / 4), c = (u % (SYN3R_PP_TW / 4)) * 4;
+            if (r >= th || c >= tw) continue;
+            const size_t i = (size_t)(y0 + r) * W + x0 + c;
+            float f[3][4];
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) {
+                const float4 v = __ldg(reinterpret_cast<const float4 *>(a.img_chw + ((size_t)p * 3 + ch) * hw + i));
+                f[ch][0] = v.x; f[ch][1] = v.y; f[ch][2] = v.z; f[ch][3] = v.w;
+            }
+            unsigned b[12];
+            float ori[12];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch) {
+                    const unsigned v = (unsigned)__float2int_rz(f[ch][j]) & 0xffu;
+                    b[3 * j + ch] = s_dil[r][c + j] ? 0u : v;
+                    ori[3 * j + ch] = __fdiv_rn(f[ch][j], 255.0f);
                 }
-                if (d) c[k] = 0;                                                              // * (1 - mask_erosion_), :1586
-            }
+            const size_t base = ((size_t)p * hw + i) * 3;
+            if (a.cond_u8) {
+                uint32_t *o = reinterpret_cast<uint32_t *>(a.cond_u8 + base);
 #pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                if (a.cond_u8) a.cond_u8[q * 3 + k] = (uint8_t)c[k];
-                if (a.cond_f32) a.cond_f32[q * 3 + k] = __fdiv_rn((float)c[k], 255.0f);       // :1590
-                if (a.cond_ori) a.cond_ori[q * 3 + k] = __fdiv_rn(a.img_u8 ? (float)a.img_u8[q * 3 + k] : f[k], 255.0f);
+                for (int k = 0; k < 3; ++k) o[k] = b[4 * k] | (b[4 * k + 1] << 8) | (b[4 * k + 2] << 16) | (b[4 * k + 3] << 24);
+            }
+            if (a.cond_f32) {
+                float4 *o = reinterpret_cast<float4 *>(a.cond_f32 + base);
+#pragma unroll
+                for (int k = 0; k < 3; ++k)
+                    o[k] = make_float4(u8_over_255(b[4 * k]), u8_over_255(b[4 * k + 1]), u8_over_255(b[4 * k + 2]), u8_over_255(b[4 * k + 3]));
+            }
+            if (a.cond_ori) {
+                float4 *o = reinterpret_cast<float4 *>(a.cond_ori + base);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) o[k] = make_float4(ori[4 * k], ori[4 * k + 1], ori[4 * k + 2], ori[4 * k + 3]);
             }
         }
     }
 
-    // ---- latent-resolution outputs: 8x8 blocks = 8 adjacent lanes x 8 rows -------------------------------------------
+    // ---- latent mask: 8x8 block count of the dilated mask, >= 13 of 64 (:1592-1596) -----------------------------------
+    if (a.latent && t < (SYN3R_PP_TW / 8) * (SYN3R_PP_TH / 8)) {
+        const int bx = t % (SYN3R_PP_TW / 8), by = t / (SYN3R_PP_TW / 8);
+        if (8 * bx < tw && 8 * by < th) {
+            unsigned cnt = 0;
 #pragma unroll
-    for (int half = 0; half < SYN3R_PP_TH / 8; ++half) {
-        const int gy0 = y0 + 8 * half;
-        const bool live = col_in && gy0 < H;                // H, W are multiples of 8: a block is inside or outside
-        unsigned cnt = live ? __popc((dil >> (8 * half)) & 0xffu) : 0u;
-        float rs = 0.0f;
-        if (a.soft_pooled && live) {
-            const float *s = a.soft + (size_t)p * hw + (size_t)gy0 * W + gx;
-            rs = __fsub_rn(1.0f, s[0]);                     // r[j] = a[j]; r[j] += a[8 i + j]  (NumPy pairwise_sum, n = 64)
+            for (int r = 0; r < 8; ++r) cnt += __popcll(*reinterpret_cast<const unsigned long long *>(&s_dil[8 * by + r][8 * bx]));
+            a.latent[((size_t)p * (H / 8) + (y0 / 8 + by)) * (W / 8) + x0 / 8 + bx] = cnt >= 13u;
+        }
+    }
+
+    // ---- pooled uncertainty: 8x8 block mean of 1 - soft in NumPy's pairwise_sum order (:1484-1487) ---------------------
+    // r[j] = a[j]; r[j] += a[8 i + j]; ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)).  A thread owns columns j = 0..3 or 4..7 of
+    // a block, its xor-1 lane partner the other four; fp32 addition is commutative, so both lanes form the same sum.
+    if (a.soft_pooled && t < 2 * (SYN3R_PP_TW / 4)) {       // warps 0-3, uniformly
+        const int by = t / (SYN3R_PP_TW / 4), c = (t % (SYN3R_PP_TW / 4)) * 4;
+        const bool live = c < tw && 8 * by < th;
+        float r[4] = {0.f, 0.f, 0.f, 0.f};
+        if (live) {
+            const float *s = a.soft + (size_t)p * hw + (size_t)(y0 + 8 * by) * W + x0 + c;
 #pragma unroll
-            for (int i = 1; i < 8; ++i) rs = __fadd_rn(rs, __fsub_rn(1.0f, s[(size_t)i * W]));
-        }
+            for (int i = 0; i < 8; ++i) {
+                const float4 v = __ldg(reinterpret_cast<const float4 *>(s + (size_t)i * W));
+                const float u[4] = {__fsub_rn(1.0f, v.x), __fsub_rn(1.0f, v.y), __fsub_rn(1.0f, v.z), __fsub_rn(1.0f, v.w)};
 #pragma unroll
-        for (int o = 1; o < 8; o <<= 1) {                   // ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)): fp add is commutative
-            cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-            rs = __fadd_rn(rs, __shfl_xor_sync(0xffffffffu, rs, o));
+                for (int j = 0; j < 4; ++j) r[j] = i ? __fadd_rn(r[j], u[j]) : u[j];
+            }
         }
-        if (live && (t & 7) == 0) {
-            const size_t lq = ((size_t)p * (H / 8) + gy0 / 8) * (W / 8) + gx / 8;
-            if (a.latent) a.latent[lq] = cnt >= 13u;        // count / 64 >= 0.2  (:1594-1596)
-            if (a.soft_pooled) a.soft_pooled[lq] = __fmul_rn(rs, 0.015625f);
-        }
+        const float half = __fadd_rn(__fadd_rn(r[0], r[1]), __fadd_rn(r[2], r[3]));
+        const float other = __shfl_xor_sync(0xffffffffu, half, 1);
+        if (live && !(t & 1))
+            a.soft_pooled[((size_t)p * (H / 8) + (y0 / 8 + by)) * (W / 8) + (x0 + c) / 8] =
+                __fmul_rn(__fadd_rn(half, other), 0.015625f);
     }
 }
 

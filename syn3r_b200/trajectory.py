@@ -163,6 +163,26 @@ class TrajectoryWarp:
         return TrajectoryOutputs(f.get("rgb_f32"), f.get("rgb_u8"), f["mask"], f.get("winner"),
                                  i.get("mask_reproj"), i.get("soft_mask_reproj"), f["status"])
 
+    def run_post(self, cond_f32: bool = False) -> dict:
+        """The reference's per-frame host block between the warp and the SVD pipeline (diffusionGS.py:1572-1597,
+        :1452-1491), for every pair, on the device (syn3r_b200.conditioning): from the forward outputs the dilated
+        hole mask, the blanked conditioning frame and the latent-resolution mask; from the consistency outputs the
+        latent mask of `mask_reproj` and the 8x8 pooled uncertainty.  Call after run(); needs want_u8."""
+        from . import conditioning as _c
+        assert self.want_u8, "run_post() blanks the uint8 frame: construct with want_u8=True"
+        if getattr(self, "out_post", None) is None:
+            self.out_post = {"fw": {}, "bw": {}}
+        want_fw = ("mask_png", "cond_f32" if cond_f32 else "cond_u8", "latent")
+        self.out_post["fw"] = {**self.out_post["fw"],
+                               **_c.condition_post_batched(self.out_fwd["mask"], img_u8=self.out_fwd["rgb_u8"],
+                                                           want=want_fw, out=self.out_post["fw"])}
+        if self.consistency:
+            self.out_post["bw"] = {**self.out_post["bw"],
+                                   **_c.condition_post_batched(self.out_inv["mask_reproj"],
+                                                               soft=self.out_inv["soft_mask_reproj"],
+                                                               want=("latent", "soft_pooled"), out=self.out_post["bw"])}
+        return self.out_post
+
     def step_host(self, rgbd_host: torch.Tensor, tgt_depth_host: Optional[torch.Tensor] = None, chunks: int = 5):
         """One end-to-end step with HOST buffers: H2D of the inputs, kernels, D2H of the host outputs into the pinned
         staging buffers.  The pairs are processed in `chunks` contiguous ranges so that the device-to-host copy of
