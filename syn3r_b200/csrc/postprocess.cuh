@@ -34,7 +34,7 @@ struct PostArgs {
 
 __device__ __forceinline__ float u8_over_255(unsigned v) { return __fdiv_rn((float)v, 255.0f); }      // :1590
 
-__global__ void __launch_bounds__(SYN3R_PP_TW)
+__global__ void __launch_bounds__(SYN3R_PP_TW, 5)
 k_condition_post(const PostArgs a) {
     // four pixels per 32-bit word, one byte (0 / 1) each
     __shared__ uint32_t s_hole_w[SYN3R_PP_TH + 4][SYN3R_PP_TW / 4 + 4];     // columns x0 - 4 .. x0 + 259
@@ -48,49 +48,89 @@ k_condition_post(const PostArgs a) {
     const int tw = min(SYN3R_PP_TW, W - x0), th = min(SYN3R_PP_TH, H - y0);        // multiples of 8
     const uint8_t *valid = a.valid + (size_t)p * hw;
 
+    // ---- first (independent of the mask, its loads overlap the staging below): pooled uncertainty, 8x8 block mean of 1 - soft in NumPy's pairwise_sum order (:1484-1487) ---------------------
+    // r[j] = a[j]; r[j] += a[8 i + j]; ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)).  A thread owns columns j = 0..3 or 4..7 of
+    // a block, its xor-1 lane partner the other four; fp32 addition is commutative, so both lanes form the same sum.
+    if (a.soft_pooled && t < 2 * (SYN3R_PP_TW / 4)) {       // warps 0-3, uniformly
+        const int by = t / (SYN3R_PP_TW / 4), c = (t % (SYN3R_PP_TW / 4)) * 4;
+        const bool live = c < tw && 8 * by < th;
+        float r[4] = {0.f, 0.f, 0.f, 0.f};
+        if (live) {
+            const float *s = a.soft + (size_t)p * hw + (size_t)(y0 + 8 * by) * W + x0 + c;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float4 v = __ldg(reinterpret_cast<const float4 *>(s + (size_t)i * W));
+                const float u[4] = {__fsub_rn(1.0f, v.x), __fsub_rn(1.0f, v.y), __fsub_rn(1.0f, v.z), __fsub_rn(1.0f, v.w)};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) r[j] = i ? __fadd_rn(r[j], u[j]) : u[j];
+            }
+        }
+        const float half = __fadd_rn(__fadd_rn(r[0], r[1]), __fadd_rn(r[2], r[3]));
+        const float other = __shfl_xor_sync(0xffffffffu, half, 1);
+        if (live && !(t & 1))
+            a.soft_pooled[((size_t)p * (H / 8) + (y0 / 8 + by)) * (W / 8) + (x0 + c) / 8] =
+                __fmul_rn(__fadd_rn(half, other), 0.015625f);
+    }
+
     // ---- stage hole = !valid with its halo; outside the image there is no hole (cv2.dilate ignores it) ----------
-    constexpr int WPR = SYN3R_PP_TW / 4 + 2;                // words per staged row: x0 - 4 .. x0 + 259
-    for (int idx = t; idx < (SYN3R_PP_TH + 4) * WPR; idx += SYN3R_PP_TW) {
-        const int r = idx / WPR, w = idx - r * WPR;
-        const int gy = y0 - 2 + r, gx = x0 - 4 + 4 * w;
-        uint32_t v = 0x01010101u;                           // covered
-        if ((unsigned)gy < (unsigned)H && (unsigned)gx < (unsigned)W)
-            v = __ldg(reinterpret_cast<const uint32_t *>(valid + (size_t)gy * W + gx));
-        s_hole_w[r][w] = __vcmpeq4(v, 0u) & 0x01010101u;
+    // thread (tx, ty) = (word column, row mod 4); every loop below has a compile-time trip count: the loads of all
+    // its iterations are in flight together
+    constexpr int WT = SYN3R_PP_TW / 4;                     // 64 words per tile row
+    const int tx = t & (WT - 1), ty = t >> 6;
+    {
+        uint32_t v[(SYN3R_PP_TH + 4) / 4];
+#pragma unroll
+        for (int n = 0; n < (SYN3R_PP_TH + 4) / 4; ++n) {
+            const int gy = y0 - 2 + ty + 4 * n, gx = x0 + 4 * tx;
+            v[n] = 0x01010101u;                             // covered
+            if ((unsigned)gy < (unsigned)H && gx < W) v[n] = __ldg(reinterpret_cast<const uint32_t *>(valid + (size_t)gy * W + gx));
+        }
+        uint32_t vh = 0x01010101u;                          // the two halo words of row t / 2 (threads 0..39)
+        const int hr = t >> 1, hgx = (t & 1) ? x0 + SYN3R_PP_TW : x0 - 4, hgy = y0 - 2 + hr;
+        if (t < 2 * (SYN3R_PP_TH + 4) && (unsigned)hgy < (unsigned)H && (unsigned)hgx < (unsigned)W)
+            vh = __ldg(reinterpret_cast<const uint32_t *>(valid + (size_t)hgy * W + hgx));
+#pragma unroll
+        for (int n = 0; n < (SYN3R_PP_TH + 4) / 4; ++n) s_hole_w[ty + 4 * n][tx + 1] = __vcmpeq4(v[n], 0u) & 0x01010101u;
+        if (t < 2 * (SYN3R_PP_TH + 4)) s_hole_w[hr][(t & 1) ? WT + 1 : 0] = __vcmpeq4(vh, 0u) & 0x01010101u;
     }
     __syncthreads();
     // separable 5x5 OR on the packed words: the neighbours at -2 .. +2 are funnel shifts over the adjacent words
-    constexpr int WT = SYN3R_PP_TW / 4;
-    for (int idx = t; idx < (SYN3R_PP_TH + 4) * WT; idx += SYN3R_PP_TW) {
-        const int r = idx / WT, j = idx - r * WT;
-        const uint32_t prev = s_hole_w[r][j], cur = s_hole_w[r][j + 1], next = s_hole_w[r][j + 2];
-        s_hor_w[r][j] = cur | __funnelshift_r(cur, next, 8) | __funnelshift_r(cur, next, 16) |
-                        __funnelshift_l(prev, cur, 8) | __funnelshift_l(prev, cur, 16);
+#pragma unroll
+    for (int n = 0; n < (SYN3R_PP_TH + 4) / 4; ++n) {
+        const int r = ty + 4 * n;
+        const uint32_t prev = s_hole_w[r][tx], cur = s_hole_w[r][tx + 1], next = s_hole_w[r][tx + 2];
+        s_hor_w[r][tx] = cur | __funnelshift_r(cur, next, 8) | __funnelshift_r(cur, next, 16) |
+                         __funnelshift_l(prev, cur, 8) | __funnelshift_l(prev, cur, 16);
     }
     __syncthreads();
-    for (int idx = t; idx < SYN3R_PP_TH * WT; idx += SYN3R_PP_TW) {
-        const int r = idx / WT, j = idx - r * WT;
-        s_dil_w[r][j] = s_hor_w[r][j] | s_hor_w[r + 1][j] | s_hor_w[r + 2][j] | s_hor_w[r + 3][j] | s_hor_w[r + 4][j];
+#pragma unroll
+    for (int n = 0; n < SYN3R_PP_TH / 4; ++n) {
+        const int r = ty + 4 * n;
+        s_dil_w[r][tx] = s_hor_w[r][tx] | s_hor_w[r + 1][tx] | s_hor_w[r + 2][tx] | s_hor_w[r + 3][tx] | s_hor_w[r + 4][tx];
     }
     __syncthreads();
 
-    // ---- mask png: 8 pixels per access (:1580-1581) -------------------------------------------------------------------
-    if (a.mask_png)
-        for (int u = t; u < SYN3R_PP_TH * (SYN3R_PP_TW / 8); u += SYN3R_PP_TW) {
-            const int r = u / (SYN3R_PP_TW / 8), c = (u % (SYN3R_PP_TW / 8)) * 8;
-            if (r < th && c < tw) {
-                uint2 d = *reinterpret_cast<const uint2 *>(&s_dil[r][c]);
+    // ---- mask png: 8 pixels per access (:1580-1581); unit (c8, r8) = 8 pixels of row r8 + 8 n ---------------------------
+    const int c8 = (t & 31) * 8, r8 = t >> 5;
+    if (a.mask_png) {
+#pragma unroll
+        for (int n = 0; n < SYN3R_PP_TH / 8; ++n) {
+            const int r = r8 + 8 * n;
+            if (r < th && c8 < tw) {
+                uint2 d = *reinterpret_cast<const uint2 *>(&s_dil[r][c8]);
                 d.x *= 255u; d.y *= 255u;                   // bytes 0 / 1 -> 0 / 255, no carries between bytes
-                *reinterpret_cast<uint2 *>(a.mask_png + (size_t)p * hw + (size_t)(y0 + r) * W + x0 + c) = d;
+                *reinterpret_cast<uint2 *>(a.mask_png + (size_t)p * hw + (size_t)(y0 + r) * W + x0 + c8) = d;
             }
         }
+    }
 
     // ---- the frame, blanked inside the dilated holes (:1586-1590) --------------------------------------------------------
     if (a.img_u8) {
         // a tile row is a flat run of 3 tw bytes; a unit = 8 pixels = 24 bytes = three 8-byte accesses, and the byte
         // mask of the unit is six byte permutations of the eight dilation bytes (byte b belongs to pixel b / 3)
-        for (int u = t; u < SYN3R_PP_TH * (SYN3R_PP_TW / 8); u += SYN3R_PP_TW) {
-            const int r = u / (SYN3R_PP_TW / 8), c = (u % (SYN3R_PP_TW / 8)) * 8;
+#pragma unroll
+        for (int n = 0; n < SYN3R_PP_TH / 8; ++n) {
+            const int r = r8 + 8 * n, c = c8;
             if (r >= th || c >= tw) continue;
             const size_t base = ((size_t)p * hw + (size_t)(y0 + r) * W + x0 + c) * 3;
             const uint2 *src = reinterpret_cast<const uint2 *>(a.img_u8 + base);
@@ -175,29 +215,6 @@ k_condition_post(const PostArgs a) {
         }
     }
 
-    // ---- pooled uncertainty: 8x8 block mean of 1 - soft in NumPy's pairwise_sum order (:1484-1487) ---------------------
-    // r[j] = a[j]; r[j] += a[8 i + j]; ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)).  A thread owns columns j = 0..3 or 4..7 of
-    // a block, its xor-1 lane partner the other four; fp32 addition is commutative, so both lanes form the same sum.
-    if (a.soft_pooled && t < 2 * (SYN3R_PP_TW / 4)) {       // warps 0-3, uniformly
-        const int by = t / (SYN3R_PP_TW / 4), c = (t % (SYN3R_PP_TW / 4)) * 4;
-        const bool live = c < tw && 8 * by < th;
-        float r[4] = {0.f, 0.f, 0.f, 0.f};
-        if (live) {
-            const float *s = a.soft + (size_t)p * hw + (size_t)(y0 + 8 * by) * W + x0 + c;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const float4 v = __ldg(reinterpret_cast<const float4 *>(s + (size_t)i * W));
-                const float u[4] = {__fsub_rn(1.0f, v.x), __fsub_rn(1.0f, v.y), __fsub_rn(1.0f, v.z), __fsub_rn(1.0f, v.w)};
-#pragma unroll
-                for (int j = 0; j < 4; ++j) r[j] = i ? __fadd_rn(r[j], u[j]) : u[j];
-            }
-        }
-        const float half = __fadd_rn(__fadd_rn(r[0], r[1]), __fadd_rn(r[2], r[3]));
-        const float other = __shfl_xor_sync(0xffffffffu, half, 1);
-        if (live && !(t & 1))
-            a.soft_pooled[((size_t)p * (H / 8) + (y0 / 8 + by)) * (W / 8) + (x0 + c) / 8] =
-                __fmul_rn(__fadd_rn(half, other), 0.015625f);
-    }
 }
 
 }  // namespace syn3r
