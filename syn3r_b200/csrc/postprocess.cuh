@@ -48,28 +48,28 @@ k_condition_post(const PostArgs a) {
     const int tw = min(SYN3R_PP_TW, W - x0), th = min(SYN3R_PP_TH, H - y0);        // multiples of 8
     const uint8_t *valid = a.valid + (size_t)p * hw;
 
-    // ---- first (independent of the mask, its loads overlap the staging below): pooled uncertainty, 8x8 block mean of 1 - soft in NumPy's pairwise_sum order (:1484-1487) ---------------------
-    // r[j] = a[j]; r[j] += a[8 i + j]; ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)).  A thread owns columns j = 0..3 or 4..7 of
-    // a block, its xor-1 lane partner the other four; fp32 addition is commutative, so both lanes form the same sum.
-    if (a.soft_pooled && t < 2 * (SYN3R_PP_TW / 4)) {       // warps 0-3, uniformly
-        const int by = t / (SYN3R_PP_TW / 4), c = (t % (SYN3R_PP_TW / 4)) * 4;
+    // ---- first (independent of the mask; its loads overlap the staging below): pooled uncertainty, the 8x8 block mean
+    //      of 1 - soft in NumPy's pairwise_sum order (:1484-1487):  r[j] = a[j]; r[j] += a[8 i + j];
+    //      ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)).  A thread owns two adjacent columns of a block (all 256 threads load),
+    //      lanes xor 1 and xor 2 hold the other pairs; fp32 addition is commutative, so every lane forms the same sums.
+    if (a.soft_pooled) {
+        const int by = t >> 7, c = (t & 127) * 2;
         const bool live = c < tw && 8 * by < th;
-        float r[4] = {0.f, 0.f, 0.f, 0.f};
+        float r0 = 0.f, r1 = 0.f;
         if (live) {
             const float *s = a.soft + (size_t)p * hw + (size_t)(y0 + 8 * by) * W + x0 + c;
+            float2 v[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const float4 v = __ldg(reinterpret_cast<const float4 *>(s + (size_t)i * W));
-                const float u[4] = {__fsub_rn(1.0f, v.x), __fsub_rn(1.0f, v.y), __fsub_rn(1.0f, v.z), __fsub_rn(1.0f, v.w)};
+            for (int i = 0; i < 8; ++i) v[i] = __ldg(reinterpret_cast<const float2 *>(s + (size_t)i * W));
+            r0 = __fsub_rn(1.0f, v[0].x); r1 = __fsub_rn(1.0f, v[0].y);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) r[j] = i ? __fadd_rn(r[j], u[j]) : u[j];
-            }
+            for (int i = 1; i < 8; ++i) { r0 = __fadd_rn(r0, __fsub_rn(1.0f, v[i].x)); r1 = __fadd_rn(r1, __fsub_rn(1.0f, v[i].y)); }
         }
-        const float half = __fadd_rn(__fadd_rn(r[0], r[1]), __fadd_rn(r[2], r[3]));
-        const float other = __shfl_xor_sync(0xffffffffu, half, 1);
-        if (live && !(t & 1))
-            a.soft_pooled[((size_t)p * (H / 8) + (y0 / 8 + by)) * (W / 8) + (x0 + c) / 8] =
-                __fmul_rn(__fadd_rn(half, other), 0.015625f);
+        const float pair = __fadd_rn(r0, r1);
+        const float quad = __fadd_rn(pair, __shfl_xor_sync(0xffffffffu, pair, 1));
+        const float all8 = __fadd_rn(quad, __shfl_xor_sync(0xffffffffu, quad, 2));
+        if (live && !(t & 3))
+            a.soft_pooled[((size_t)p * (H / 8) + (y0 / 8 + by)) * (W / 8) + (x0 + c) / 8] = __fmul_rn(all8, 0.015625f);
     }
 
     // ---- stage hole = !valid with its halo; outside the image there is no hole (cv2.dilate ignores it) ----------
