@@ -83,3 +83,24 @@ def test_post_float_frame_truncates_like_np_uint8():
     r = po.post_backward(f, m, s)
     for k in ("mask_png", "cond", "cond_ori", "latent_mask", "soft_pooled"):
         assert np.array_equal(o[k], r[k]), k
+
+
+def test_trajectory_run_post_matches_oracle_on_the_plan_outputs():
+    """TrajectoryWarp.run() -> run_post(): the reference's caller block applied to every pair's warped frame, hole
+    mask, reprojection mask and soft mask, checked against the oracle fed with the plan's own outputs."""
+    from syn3r_b200 import synth, trajectory, warp as w
+    S, T, H, W = 2, 3, 64, 96
+    tr = synth.make_trajectory(S, T, H, W, seed=91)
+    tw = trajectory.from_synth(tr, want_u8=True, want_f32=False)
+    tw.upload(torch.from_numpy(w.pack_rgbd(tr.rgb, tr.depth)), torch.from_numpy(tr.depth_tgt))
+    out = tw.run()
+    post = tw.run_post()
+    torch.cuda.synchronize()
+    for p in range(tw.P):
+        r = po.post_forward(out.rgb_u8[p].cpu().numpy(), out.mask[p].cpu().numpy().astype(bool))
+        assert np.array_equal(post["fw"]["mask_png"][p].cpu().numpy(), r["mask_png"][..., 0])
+        assert np.array_equal(post["fw"]["cond_u8"][p].cpu().numpy(), r["cond_u8"])
+        assert np.array_equal(post["fw"]["latent"][p].cpu().numpy().astype(np.float64), r["latent_mask"])
+        dil = po.dilate5(~out.mask_reproj[p].cpu().numpy().astype(bool))
+        assert np.array_equal(post["bw"]["latent"][p].cpu().numpy().astype(np.float64), po.latent_mask(dil))
+        assert np.array_equal(post["bw"]["soft_pooled"][p].cpu().numpy(), po.pool_soft(out.soft_mask_reproj[p].cpu().numpy()))
