@@ -349,12 +349,13 @@ def run_ours(args):
     # frame + hole mask (forward_warp.py:182) and the consumed inverse_warp keys mask_reproj + soft_mask_reproj
     # (diffusionGS.py:1346-1347); the winner index (extension) is computed and stays on the device.
     # `e2e_all_outputs`: the `value` plan itself with every output (fp32 colour + winner) copied back.
-    e2e, e2e_all = None, None
+    e2e, e2e_all, e2e_post = None, None, None
     if not args.no_e2e:
         def measure(plan, how):
             g_wire = g_plan = None
             if world > 1:                                   # the plan's own wire: uint8 frames for the reference-facing plan
-                g_wire = sharding.compact_wire(plan.out_fwd, plan.out_inv)
+                g_wire = ({k: plan.out_post[k] for k in plan.host_outputs if k in plan.out_post} if plan.post
+                          else sharding.compact_wire(plan.out_fwd, plan.out_inv))
                 g_plan = gather if plan is tw else sharding.FrameGather(g_wire, [plan.P] * world, dst=0)
 
             def step_e2e():
@@ -382,6 +383,17 @@ def run_ours(args):
                               "reference's forward_warp / inverse_warp return to their callers, overlapping the next "
                               "range (PCIe-bound)")
         assert int(tw_ref.out_fwd["status"].max().item()) == 0
+        del tw_ref
+        # the same step when the callers' post-processing also runs on the device: only what the SVD
+        # pipeline consumes travels back - the blanked uint8 frame, the two latent masks, the pooled uncertainty
+        if H % 8 == 0 and W % 8 == 0:
+            tw_post = trajectory.from_synth(tr, pairs=(ps, pt), want_f32=False, want_u8=True, want_winner=True,
+                                            pinned_host=True, post=True,
+                                            host_outputs=("post_cond_u8", "post_latent", "post_latent_reproj", "post_soft_pooled"))
+            e2e_post = measure(tw_post, "as `e2e`, plus k_condition_post on every pair range; D2H of the blanked uint8 frame, "
+                                        "the latent masks of the hole and reprojection masks and the pooled uncertainty "
+                                        "(diffusionGS.py:1572-1597, :1452-1491 on the device)")
+            del tw_post
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -392,7 +404,7 @@ def run_ours(args):
                 "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64 projection / block-floating-point i32 accumulate / f32 consistency", "data": "synthetic",
                 "config": workload_desc(args, S, T, H, W, len(ps)), "clocks": clocks, "e2e": e2e,
-                "e2e_all_outputs": e2e_all,
+                "e2e_all_outputs": e2e_all, "e2e_conditioning": e2e_post,
                 "gpu_launches": args.steps * tw.launches_per_run(), "roofline": roofline, "cpu_baseline": cpu,
                 "pair_mpix_per_s": world * args.steps * len(ps) * H * W / 1e6 / (total_ms / 1e3)}
         if gather_info is not None:

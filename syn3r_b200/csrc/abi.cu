@@ -246,6 +246,8 @@ int syn3r_forward_warp_batched(const float *rgbd, const double *depth64, const u
                                float *out_rgb_f32, uint8_t *out_rgb_u8, uint8_t *out_mask, int32_t *out_winner,
                                double *out_flow, int32_t *out_status, void *workspace, size_t workspace_bytes,
                                void *stream) {
+    // an empty batch is a valid no-op (the reference's per-frame loop simply does not run): nothing is read or written
+    if (P == 0 && (n_slots == 0 || pair_slot == nullptr)) return SYN3R_OK;
     SYN3R_REQUIRE(rgbd && Kinv_src && pair_par && pair_src && out_mask && workspace, "null required pointer");
     SYN3R_REQUIRE(S > 0 && P > 0 && n_slots > 0 && H > 0 && W > 0, "non-positive size");
     SYN3R_REQUIRE((size_t)S * H * W < 0x7fffffffull, "S*H*W must fit the 31-bit winner index");

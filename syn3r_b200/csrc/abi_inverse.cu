@@ -60,6 +60,7 @@ int syn3r_inverse_warp_batched(const float *src_img, const float *src_depth, int
                                const int32_t *pair_src, const int32_t *pair_tgt, int P, int H, int W,
                                float bandwidth, float thr_depth, float thr_depth_strict,
                                const syn3r_inv_outputs *out, void *workspace, size_t workspace_bytes, void *stream) {
+    if (P == 0) return SYN3R_OK;                            // empty batch: a valid no-op
     SYN3R_REQUIRE(src_depth && tgt_depth && K && Kinv && pair_P && pair_src && pair_tgt && out,
                   "null required pointer");
     SYN3R_REQUIRE(src_img || !(out->warped_img || out->warped_masked_img), "colour outputs need src_img");

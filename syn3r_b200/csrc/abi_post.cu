@@ -8,6 +8,7 @@ extern "C" {
 int syn3r_condition_post_batched(const uint8_t *valid, const uint8_t *img_u8, const float *img_chw, const float *soft,
                                  int P, int H, int W, uint8_t *out_mask_png, uint8_t *out_cond_u8, float *out_cond_f32,
                                  float *out_cond_ori, uint8_t *out_latent, float *out_soft_pooled, void *stream) {
+    if (P == 0) return SYN3R_OK;                            // empty batch: a valid no-op
     SYN3R_REQUIRE(valid != nullptr, "the valid mask is required");
     SYN3R_REQUIRE(P >= 0 && H > 0 && W > 0, "bad sizes");
     // the reference reshapes to (H/8, 8, W/8, 8) (diffusionGS.py:1593): sizes that do not divide raise there too
@@ -16,7 +17,6 @@ int syn3r_condition_post_batched(const uint8_t *valid, const uint8_t *img_u8, co
     SYN3R_REQUIRE(!(out_cond_u8 || out_cond_f32 || out_cond_ori) || img_u8 || img_chw, "frame outputs need a frame input");
     SYN3R_REQUIRE(!out_soft_pooled || soft, "soft_pooled needs the soft mask");
     SYN3R_REQUIRE(P <= 65535, "at most 65535 frames per call");
-    if (P == 0) return SYN3R_OK;
     PostArgs a{valid, img_u8, img_chw, soft, H, W, out_mask_png, out_cond_u8, out_cond_f32, out_cond_ori, out_latent,
                out_soft_pooled};
     dim3 grid((W + SYN3R_PP_TW - 1) / SYN3R_PP_TW, (H + SYN3R_PP_TH - 1) / SYN3R_PP_TH, P);

@@ -36,7 +36,7 @@ class TrajectoryWarp:
     def __init__(self, S: int, T: int, H: int, W: int, pair_src: Sequence[int], pair_tgt: Sequence[int], *,
                  device=None, consistency: bool = True, want_f32: bool = True, want_u8: bool = False,
                  want_winner: bool = True, bandwidth: float = 20.0, pinned_host: bool = False,
-                 host_outputs: Optional[Sequence[str]] = None):
+                 host_outputs: Optional[Sequence[str]] = None, post: bool = False):
         self.S, self.T, self.H, self.W = S, T, H, W
         self.pair_src_h = np.asarray(pair_src, np.int32)
         self.pair_tgt_h = np.asarray(pair_tgt, np.int32)
@@ -67,11 +67,16 @@ class TrajectoryWarp:
         if consistency:
             self.out_inv["mask_reproj"] = torch.empty((P, H, W), dtype=torch.uint8, device=d)
             self.out_inv["soft_mask_reproj"] = torch.empty((P, H, W), dtype=torch.float32, device=d)
+        # the callers' per-frame post-processing (diffusionGS.py:1572-1597, :1452-1491) as part of every run
+        self.post = bool(post)
+        self.out_post = {}
+        if self.post:
+            self._alloc_post()
         # outputs that travel to the host in step_host()/download(); None = every output.  The reference's own
         # return values are ("rgb_u8", "mask") from forward_warp (forward_warp.py:182) and the consumed keys
         # ("mask_reproj", "soft_mask_reproj") of inverse_warp (diffusionGS.py:1346-1347); the rest are extensions
         # (fp32 colour, winner index) that device-side consumers read in place.
-        allk = list(self.out_fwd) + list(self.out_inv)
+        allk = list(self.out_fwd) + list(self.out_inv) + list(self.out_post)
         self.host_outputs = allk if host_outputs is None else [k for k in allk if k in set(host_outputs) | {"status"}]
         assert host_outputs is None or set(host_outputs) <= set(allk), f"unknown output in {host_outputs}"
         self.pinned = None
@@ -111,8 +116,31 @@ class TrajectoryWarp:
         for k, v in self._host_items():
             self.pinned["out_" + k] = pin(tuple(v.shape), v.dtype)
 
+    def _alloc_post(self):
+        assert self.want_u8, "the post-processing blanks the uint8 frame: construct with want_u8=True"
+        assert self.H % 8 == 0 and self.W % 8 == 0, "post-processing needs H and W to be multiples of 8"
+        P, H, W, d = self.P, self.H, self.W, self.dev
+        self.out_post = {"post_mask_png": torch.empty((P, H, W), dtype=torch.uint8, device=d),
+                         "post_cond_u8": torch.empty((P, H, W, 3), dtype=torch.uint8, device=d),
+                         "post_latent": torch.empty((P, H // 8, W // 8), dtype=torch.uint8, device=d)}
+        if self.consistency:
+            self.out_post["post_latent_reproj"] = torch.empty((P, H // 8, W // 8), dtype=torch.uint8, device=d)
+            self.out_post["post_soft_pooled"] = torch.empty((P, H // 8, W // 8), dtype=torch.float32, device=d)
+
+    def _post(self, sl=slice(None)):
+        from . import conditioning as _c
+        o = self.out_post
+        _c.condition_post_batched(self.out_fwd["mask"][sl], img_u8=self.out_fwd["rgb_u8"][sl],
+                                  want=("mask_png", "cond_u8", "latent"),
+                                  out={"mask_png": o["post_mask_png"][sl], "cond_u8": o["post_cond_u8"][sl],
+                                       "latent": o["post_latent"][sl]})
+        if self.consistency:
+            _c.condition_post_batched(self.out_inv["mask_reproj"][sl], soft=self.out_inv["soft_mask_reproj"][sl],
+                                      want=("latent", "soft_pooled"),
+                                      out={"latent": o["post_latent_reproj"][sl], "soft_pooled": o["post_soft_pooled"][sl]})
+
     def _host_items(self):
-        both = {**self.out_fwd, **self.out_inv}
+        both = {**self.out_fwd, **self.out_inv, **self.out_post}
         return [(k, both[k]) for k in self.host_outputs]
 
     def upload(self, rgbd_host: torch.Tensor, tgt_depth_host: Optional[torch.Tensor] = None):
@@ -155,6 +183,8 @@ class TrajectoryWarp:
         else:
             self._forward(sl)
             self._inverse(sl)
+        if self.post:
+            self._post(sl)
 
     def run(self) -> TrajectoryOutputs:
         """Enqueue forward warp (+ consistency masks) for all pairs on the current stream."""
@@ -163,25 +193,20 @@ class TrajectoryWarp:
         return TrajectoryOutputs(f.get("rgb_f32"), f.get("rgb_u8"), f["mask"], f.get("winner"),
                                  i.get("mask_reproj"), i.get("soft_mask_reproj"), f["status"])
 
-    def run_post(self, cond_f32: bool = False) -> dict:
+    def run_post(self) -> dict:
         """The reference's per-frame host block between the warp and the SVD pipeline (diffusionGS.py:1572-1597,
         :1452-1491), for every pair, on the device (syn3r_b200.conditioning): from the forward outputs the dilated
         hole mask, the blanked conditioning frame and the latent-resolution mask; from the consistency outputs the
-        latent mask of `mask_reproj` and the 8x8 pooled uncertainty.  Call after run(); needs want_u8."""
-        from . import conditioning as _c
-        assert self.want_u8, "run_post() blanks the uint8 frame: construct with want_u8=True"
-        if getattr(self, "out_post", None) is None:
-            self.out_post = {"fw": {}, "bw": {}}
-        want_fw = ("mask_png", "cond_f32" if cond_f32 else "cond_u8", "latent")
-        self.out_post["fw"] = {**self.out_post["fw"],
-                               **_c.condition_post_batched(self.out_fwd["mask"], img_u8=self.out_fwd["rgb_u8"],
-                                                           want=want_fw, out=self.out_post["fw"])}
+        latent mask of `mask_reproj` and the 8x8 pooled uncertainty.  Call after run() (a plan built with post=True
+        does it inside every run); needs want_u8."""
+        if not self.out_post:
+            self._alloc_post()
+        self._post()
+        o = self.out_post
+        res = {"fw": {"mask_png": o["post_mask_png"], "cond_u8": o["post_cond_u8"], "latent": o["post_latent"]}, "bw": {}}
         if self.consistency:
-            self.out_post["bw"] = {**self.out_post["bw"],
-                                   **_c.condition_post_batched(self.out_inv["mask_reproj"],
-                                                               soft=self.out_inv["soft_mask_reproj"],
-                                                               want=("latent", "soft_pooled"), out=self.out_post["bw"])}
-        return self.out_post
+            res["bw"] = {"latent": o["post_latent_reproj"], "soft_pooled": o["post_soft_pooled"]}
+        return res
 
     def step_host(self, rgbd_host: torch.Tensor, tgt_depth_host: Optional[torch.Tensor] = None, chunks: int = 5):
         """One end-to-end step with HOST buffers: H2D of the inputs, kernels, D2H of the host outputs into the pinned
@@ -222,7 +247,7 @@ class TrajectoryWarp:
     def launches_per_run(self) -> int:
         """Kernels of libsyn3r_warp.so per run() (memsets not counted): k_src_stats, k_fwd_prep (bounds), k_fwd_prep (pruned max z'),
         k_fwd_finalize, k_fwd_tile_fx, k_fwd_tile (redo list, normally empty) (+ k_reproj_masks)."""
-        return 6 + (1 if self.consistency else 0)
+        return 6 + (1 if self.consistency else 0) + ((2 if self.consistency else 1) if self.post else 0)
 
 
 def from_synth(traj, pairs=None, **kw) -> TrajectoryWarp:

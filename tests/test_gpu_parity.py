@@ -307,12 +307,29 @@ def test_lean_reproj_mask_equals_err_below_bandwidth(bw):
         assert np.array_equal(np.isnan(a), np.isnan(b)) and np.max(np.abs(a[fin] - b[fin]), initial=0) <= 2e-6
 
 
+def test_empty_batch_is_a_no_op():
+    """Zero pairs: the reference's per-frame loop does not run; the batched entry points return empty outputs."""
+    from syn3r_b200 import conditioning, warp as w
+    tr = synth.make_trajectory(1, 1, 8, 16, seed=1)
+    e = np.zeros((0,), np.int32)
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    Kinv, par = w.forward_pair_params(tr.pose_src, tr.pose_tgt, tr.K, None, e, e)
+    o = w.forward_warp_batched(up(w.pack_rgbd(tr.rgb, tr.depth)), up(Kinv), up(par.reshape(0, 24)), up(e), want_winner=True)
+    assert o["mask"].shape == (0, 8, 16) and o["winner"].shape == (0, 8, 16)
+    i = w.inverse_warp_batched(None, up(tr.depth), up(tr.depth_tgt), tr.K.astype(np.float32),
+                               up(np.zeros((0, 2, 16), np.float32)), up(e), up(e), want=("mask_reproj", "soft_mask_reproj"))
+    assert i["mask_reproj"].shape == (0, 8, 16)
+    c = conditioning.condition_post_batched(torch.zeros((0, 8, 16), dtype=torch.uint8, device="cuda"))
+    assert c["latent"].shape == (0, 1, 2)
+    torch.cuda.synchronize()
+
+
 def test_step_host_matches_run():
     """The pipelined end-to-end step (H2D, kernels in pair ranges, overlapped D2H) == run() + download()."""
     from syn3r_b200 import trajectory, warp as w
     S, T, H, W = 2, 4, 48, 160
     tr = synth.make_trajectory(S, T, H, W, seed=71)
-    tw = trajectory.from_synth(tr, want_u8=True, pinned_host=True)
+    tw = trajectory.from_synth(tr, want_u8=True, pinned_host=True, post=True)
     rgbd_h, tgt_h = torch.from_numpy(w.pack_rgbd(tr.rgb, tr.depth)), torch.from_numpy(tr.depth_tgt)
     tw.upload(rgbd_h, tgt_h)
     tw.run()
