@@ -8,8 +8,9 @@
 // staged in shared memory with its 2-pixel halo (32-bit loads), dilated separably (5-wide OR along x, then along y)
 // into a byte plane, and every input and output byte is touched once with 8- or 16-byte accesses: the uint8 frame
 // as a flat run of 768 bytes per tile row (byte b belongs to pixel b / 3), the mask png 8 pixels at a time, the
-// soft mask as float4 (a thread owns 4 of a block's 8 columns, its lane partner the other 4).  Algorithmic bytes per pixel: valid 1 + image 3 (uint8) or 12 (fp32) in;
-// mask png 1, blanked frame 3 (uint8) and / or 12 (fp32), soft 4 in; 1/64 + 4/64 for the latent outputs.
+// soft mask as float2 (a thread owns 2 of a block's 8 columns, its xor-1 / xor-2 lanes the other pairs).
+// Algorithmic bytes per pixel: valid 1 + image 3 (uint8) or 12 (fp32) in; mask png 1, blanked frame 3 (uint8)
+// and / or 12 (fp32), soft 4 in; 1/64 + 4/64 for the latent outputs.
 #pragma once
 #include "common.cuh"
 

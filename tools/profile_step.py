@@ -14,7 +14,8 @@ S, T, H, W = synth.CONFIGS[cfg]
 if len(sys.argv) > 2:
     T = int(sys.argv[2])
 tr = synth.make_trajectory(S, T, H, W, seed=0)
-tw = trajectory.from_synth(tr, want_f32=True, want_u8=False, want_winner=True)
+post = os.environ.get("SYN3R_PROFILE_POST", "0") == "1"     # also the callers' post-processing (k_condition_post)
+tw = trajectory.from_synth(tr, want_f32=True, want_u8=post, want_winner=True, post=post)
 tw.upload(torch.from_numpy(w.pack_rgbd(tr.rgb, tr.depth)), torch.from_numpy(tr.depth_tgt))
 for _ in range(2):
     tw.run()
