@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SYN3R_ABI_VERSION 6
+#define SYN3R_ABI_VERSION 7
 
 enum {
     SYN3R_OK = 0,
@@ -180,6 +180,14 @@ int syn3r_transform_points(const float *pts, const float *T, int H, int W, float
 int syn3r_condition_post_batched(const uint8_t *valid, const uint8_t *img_u8, const float *img_chw, const float *soft,
                                  int P, int H, int W, uint8_t *out_mask_png, uint8_t *out_cond_u8, float *out_cond_f32,
                                  float *out_cond_ori, uint8_t *out_latent, float *out_soft_pooled, void *stream);
+
+/* Score of a pose candidate (model/diffusionGS.py:759-761): out_mean[p] = mean over the frame of
+ * 1 - soft[p] (float32 element arithmetic as in the reference, deterministic fixed-order reduction).  soft [P,H,W] is
+ * the soft_mask_reproj output of syn3r_inverse_warp_batched for the (nearest reference, candidate) pairs.
+ * workspace: syn3r_mean_uncertainty_workspace_bytes(P) bytes, caller-owned. */
+size_t syn3r_mean_uncertainty_workspace_bytes(int P);
+int syn3r_mean_uncertainty_batched(const float *soft, int P, int H, int W, float *out_mean, void *workspace,
+                                   size_t workspace_bytes, void *stream);
 
 #ifdef __cplusplus
 }

@@ -1,5 +1,6 @@
 // abi_post.cu — extern "C" launcher of the warped-frame post-processing (include/syn3r_warp.h).
 #include "postprocess.cuh"
+#include "score.cuh"
 
 using namespace syn3r;
 
@@ -22,6 +23,26 @@ int syn3r_condition_post_batched(const uint8_t *valid, const uint8_t *img_u8, co
     dim3 grid((W + SYN3R_PP_TW - 1) / SYN3R_PP_TW, (H + SYN3R_PP_TH - 1) / SYN3R_PP_TH, P);
     k_condition_post<<<grid, SYN3R_PP_TW, 0, (cudaStream_t)stream>>>(a);
     return check_cuda(cudaGetLastError(), "k_condition_post");
+}
+
+size_t syn3r_mean_uncertainty_workspace_bytes(int P) { return P > 0 ? (size_t)P * SYN3R_SC_BLOCKS * sizeof(double) : 0; }
+
+int syn3r_mean_uncertainty_batched(const float *soft, int P, int H, int W, float *out_mean, void *workspace,
+                                   size_t workspace_bytes, void *stream) {
+    if (P == 0) return SYN3R_OK;
+    SYN3R_REQUIRE(soft && out_mean && workspace, "null required pointer");
+    SYN3R_REQUIRE(P > 0 && P <= 65535 && H > 0 && W > 0, "bad sizes");
+    SYN3R_REQUIRE(((size_t)H * W) % 4 == 0 || P == 1, "H*W must be a multiple of 4 for P > 1 (16-byte frame alignment)");
+    SYN3R_REQUIRE(((uintptr_t)soft & 15) == 0 && ((uintptr_t)workspace & 7) == 0, "soft must be 16-byte aligned");
+    if (workspace_bytes < syn3r_mean_uncertainty_workspace_bytes(P)) {
+        set_error("mean-uncertainty workspace: need %zu bytes (got %zu)", syn3r_mean_uncertainty_workspace_bytes(P), workspace_bytes);
+        return SYN3R_EWORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t hw = (size_t)H * W;
+    k_mean_uncertainty_partial<<<dim3(SYN3R_SC_BLOCKS, P), SYN3R_SC_THREADS, 0, st>>>(soft, hw, (double *)workspace);
+    k_mean_uncertainty_final<<<(P + 127) / 128, 128, 0, st>>>((const double *)workspace, P, hw, out_mean);
+    return check_cuda(cudaGetLastError(), "k_mean_uncertainty");
 }
 
 }  // extern "C"
