@@ -118,11 +118,6 @@ __device__ __forceinline__ float4 ld_keep_f4(const float4 *p, uint64_t pol) {
                  : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p), "l"(pol));
     return r;
 }
-__device__ __forceinline__ float ld_keep_f1(const float *p, uint64_t pol) {
-    float r;
-    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(r) : "l"(p), "l"(pol));
-    return r;
-}
 __device__ __forceinline__ void st_once_f4(float4 *p, float4 v, uint64_t pol) {
     asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;"
                  :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "l"(pol) : "memory");
