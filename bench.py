@@ -325,7 +325,22 @@ def run_ours(args):
         t_bw = statistics.mean(timed(post_bw, n_k, between=flush.zero_))
         b_fw = P_ * hw * 8 + P_ * (hw // 64)                  # valid 1 + frame 3 in; png 1 + blanked frame 3 + latent out
         b_bw = P_ * hw * 5 + P_ * (hw // 64) * 5              # valid 1 + soft 4 in; latent 1 + pooled 4 per 8x8 block out
+        # uncertainty fusion of the T - 2 interior frames (diffusionGS.py:821-854), 28 B in + 12 B out
+        Nf = max(T - 2, 1)
+        c_ori = torch.rand((Nf, H, W, 3), device=dev)
+        g_img = torch.rand((Nf, H, W, 3), device=dev)
+        s_ori = torch.rand((Nf, H, W), device=dev)
+        o_fu = {}
+
+        def fuse():
+            o_fu.update(conditioning.fuse_uncertainty_batched(c_ori, g_img, s_ori, want=("cond_image", "masks"), out=o_fu))
+        fuse()
+        t_fu = statistics.mean(timed(fuse, n_k, between=flush.zero_))
+        b_fu = Nf * hw * 40 + Nf * (hw // 64) * 4
+        del c_ori, g_img, s_ori
         post = {"kernel": "k_condition_post", "forward_branch_ms": t_fw, "backward_branch_ms": t_bw,
+                "fusion": {"kernel": "k_fuse_uncertainty", "frames": Nf, "ms": t_fu, "algorithmic_bytes": b_fu,
+                           "achieved_GBps": b_fu / t_fu / 1e6, "frac": b_fu / t_fu / 1e6 / peak},
                 "forward_branch": {"algorithmic_bytes": b_fw, "achieved_GBps": b_fw / t_fw / 1e6, "frac": b_fw / t_fw / 1e6 / peak},
                 "backward_branch": {"algorithmic_bytes": b_bw, "achieved_GBps": b_bw / t_bw / 1e6, "frac": b_bw / t_bw / 1e6 / peak},
                 "scope": "diffusionGS.py:1572-1597 / :1452-1491 for all pairs; not part of `value` (SURVEY 8f rank 1)"}

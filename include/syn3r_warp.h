@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SYN3R_ABI_VERSION 7
+#define SYN3R_ABI_VERSION 8
 
 enum {
     SYN3R_OK = 0,
@@ -180,6 +180,14 @@ int syn3r_transform_points(const float *pts, const float *T, int H, int W, float
 int syn3r_condition_post_batched(const uint8_t *valid, const uint8_t *img_u8, const float *img_chw, const float *soft,
                                  int P, int H, int W, uint8_t *out_mask_png, uint8_t *out_cond_u8, float *out_cond_f32,
                                  float *out_cond_ori, uint8_t *out_latent, float *out_soft_pooled, void *stream);
+
+/* Uncertainty fusion of N frames (model/diffusionGS.py:821-854 and the clip of :876):
+ *   conf = exp(-(|cond_ori - gs| / 0.5)^3) * (cond_ori.sum(-1) > 0);  unc = 1 - conf * (1 - soft_ori)   [float64]
+ *   out_masks [N,H/8,W/8] f32 = 8x8 block mean of unc;  out_cond [N,H,W,3] f32 = clip(unc > 0.5 ? gs : cond_ori, 0, 1);
+ *   out_unc [N,H,W] f64 = geo_inten_uncertainty.  cond_ori, gs [N,H,W,3] f32; soft_ori [N,H,W] f32 = 1 - soft_mask_reproj.
+ * Any output may be NULL (not all).  H and W must be multiples of 8. */
+int syn3r_fuse_uncertainty_batched(const float *cond_ori, const float *gs, const float *soft_ori, int N, int H, int W,
+                                   float *out_cond, float *out_masks, double *out_unc, void *stream);
 
 /* Score of a pose candidate (model/diffusionGS.py:759-761): out_mean[p] = mean over the frame of
  * 1 - soft[p] (float32 element arithmetic as in the reference, deterministic fixed-order reduction).  soft [P,H,W] is

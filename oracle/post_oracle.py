@@ -73,3 +73,35 @@ def post_backward(warped_f32: np.ndarray, mask2: np.ndarray, soft: np.ndarray) -
                 cond_ori=(warped_f32 / np.float32(255.0)).astype(np.float32), latent_mask=latent_mask(dil),
                 masks_ero=np.repeat(dil.astype(np.uint8)[..., None], 3, axis=2),
                 soft_ori=(np.float32(1) - soft).astype(np.float32), soft_pooled=pool_soft(soft))
+
+
+def fuse_uncertainty(cond_ori: np.ndarray, gs: np.ndarray, soft_ori: np.ndarray) -> dict:
+    """Uncertainty fusion of /root/reference/model/diffusionGS.py:821-854 and the clip of :876,
+    every intermediate in the dtype NumPy gives it there:
+      s      = (c0 + c1) + c2                      float32      (:833 `cond_image_ori.sum(axis=-1)`)
+      nrm    = sqrt(((d0 d0 + d1 d1) + d2 d2))     float32      (np.linalg.norm over the last axis, d = cond - gs)
+      conf   = exp(-(nrm / 0.5) ** 3)              float32, then * (1 - uncertainty_mask) [int64] -> float64
+      geo    = conf * (1 - soft_ori)               float64 * float32 -> float64          (:836)
+      unc    = 1 - geo                             float64                               (:838)
+      masks  = 8x8 block mean of unc (float64, NumPy pairwise order), cast float32      (:841-848)
+      cond   = clip(where(unc > 0.5, gs, cond_ori), 0, 1)                                (:854, :876)
+    cond_ori, gs (N,H,W,3) float32; soft_ori (N,H,W) float32 (= 1 - soft_mask_reproj)."""
+    c, g = cond_ori.astype(np.float32), gs.astype(np.float32)
+    s = ((c[..., 0] + c[..., 1]) + c[..., 2]).astype(np.float32)
+    d = (c - g).astype(np.float32)
+    sq = (d * d).astype(np.float32)
+    nrm = np.sqrt(((sq[..., 0] + sq[..., 1]) + sq[..., 2]).astype(np.float32)).astype(np.float32)
+    t = (nrm / np.float32(0.5)).astype(np.float32)
+    conf32 = np.exp(-((t * t).astype(np.float32) * t).astype(np.float32)).astype(np.float32)
+    conf = conf32.astype(np.float64) * (s > 0).astype(np.float64)
+    geo = conf * (np.float32(1) - soft_ori.astype(np.float32)).astype(np.float64)
+    unc = 1.0 - geo
+    N, H, W = unc.shape
+    u = unc.reshape(N, H // 8, 8, W // 8, 8)
+    r = u[:, :, 0].copy()
+    for i in range(1, 8):
+        r = r + u[:, :, i]
+    tot = ((r[..., 0] + r[..., 1]) + (r[..., 2] + r[..., 3])) + ((r[..., 4] + r[..., 5]) + (r[..., 6] + r[..., 7]))
+    masks = (tot / 64.0).astype(np.float32)
+    cond = np.clip(np.where(unc[..., None] > 0.5, g, c), 0, 1).astype(np.float32)
+    return dict(masks=masks, cond_image=cond, geo_inten_uncertainty=unc[..., None])

@@ -90,3 +90,31 @@ def post_backward(warped_frame2: np.ndarray, mask2: np.ndarray, soft_mask_reproj
                 cond=o["cond_f32"][0].cpu().numpy(), cond_ori=o["cond_ori"][0].cpu().numpy(),
                 latent_mask=o["latent"][0].cpu().numpy().astype(np.float64),
                 soft_pooled=o["soft_pooled"][0].cpu().numpy())
+
+
+def fuse_uncertainty_batched(cond_ori: torch.Tensor, gs: torch.Tensor, soft_ori: torch.Tensor, *,
+                             want: Sequence[str] = ("cond_image", "masks"),
+                             out: Optional[Dict[str, torch.Tensor]] = None) -> Dict[str, torch.Tensor]:
+    """Uncertainty fusion of diffusionGS.py:821-854 + the clip of :876 on the device.
+    cond_ori, gs [N,H,W,3] f32; soft_ori [N,H,W] f32 (= 1 - soft_mask_reproj): CUDA tensors.  `want` picks from
+    cond_image [N,H,W,3] f32, masks [N,H/8,W/8] f32, geo_inten_uncertainty [N,H,W] f64."""
+    L = nat.lib()
+    assert set(want) <= {"cond_image", "masks", "geo_inten_uncertainty"} and len(want) > 0
+    N, H, W, three = cond_ori.shape
+    assert three == 3 and gs.shape == cond_ori.shape and soft_ori.shape == (N, H, W)
+    assert cond_ori.dtype == gs.dtype == soft_ori.dtype == torch.float32
+    assert H % 8 == 0 and W % 8 == 0, "H and W must be multiples of 8 (diffusionGS.py:843 reshapes to 8x8 blocks)"
+    shapes = {"cond_image": ((N, H, W, 3), torch.float32), "masks": ((N, H // 8, W // 8), torch.float32),
+              "geo_inten_uncertainty": ((N, H, W), torch.float64)}
+    o = dict(out or {})
+    for k in want:
+        shp, dt = shapes[k]
+        if o.get(k) is None:
+            o[k] = torch.empty(shp, dtype=dt, device=cond_ori.device)
+        assert o[k].shape == torch.Size(shp) and o[k].dtype == dt and o[k].is_contiguous()
+    ptr = lambda k: nat.ptr(o[k]) if k in want else None  # noqa: E731
+    nat.check(L.syn3r_fuse_uncertainty_batched(nat.ptr(cond_ori), nat.ptr(gs), nat.ptr(soft_ori), N, H, W, ptr("cond_image"),
+                                               ptr("masks"), ptr("geo_inten_uncertainty"),
+                                               torch.cuda.current_stream(cond_ori.device).cuda_stream),
+              "syn3r_fuse_uncertainty_batched")
+    return {k: o[k] for k in want}

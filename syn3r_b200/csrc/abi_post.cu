@@ -25,6 +25,18 @@ int syn3r_condition_post_batched(const uint8_t *valid, const uint8_t *img_u8, co
     return check_cuda(cudaGetLastError(), "k_condition_post");
 }
 
+int syn3r_fuse_uncertainty_batched(const float *cond_ori, const float *gs, const float *soft_ori, int N, int H, int W,
+                                   float *out_cond, float *out_masks, double *out_unc, void *stream) {
+    if (N == 0) return SYN3R_OK;
+    SYN3R_REQUIRE(cond_ori && gs && soft_ori, "null required pointer");
+    SYN3R_REQUIRE(N > 0 && N <= 65535 && H > 0 && W > 0, "bad sizes");
+    SYN3R_REQUIRE(H % 8 == 0 && W % 8 == 0, "H and W must be multiples of 8 (latent grid of 8x8 blocks)");
+    SYN3R_REQUIRE(out_cond || out_masks || out_unc, "no output requested");
+    k_fuse_uncertainty<<<dim3((W + 255) / 256, H / 8, N), 128, 0, (cudaStream_t)stream>>>(cond_ori, gs, soft_ori, H, W, out_cond,
+                                                                                       out_masks, out_unc);
+    return check_cuda(cudaGetLastError(), "k_fuse_uncertainty");
+}
+
 size_t syn3r_mean_uncertainty_workspace_bytes(int P) { return P > 0 ? (size_t)P * SYN3R_SC_BLOCKS * sizeof(double) : 0; }
 
 int syn3r_mean_uncertainty_batched(const float *soft, int P, int H, int W, float *out_mean, void *workspace,

@@ -39,3 +39,24 @@ def test_pool_soft_matches_numpy_mean_order():
     s = rng.random((80, 136), dtype=np.float32)
     u = (1 - s).reshape(10, 8, 17, 8).transpose(0, 2, 1, 3).reshape(10, 17, 64)
     assert np.array_equal(np.mean(u, axis=2), po.pool_soft(s))
+
+
+FUSION = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "fusion_*.npz")))
+
+
+@pytest.mark.parametrize("name", FUSION)
+def test_fuse_uncertainty_oracle_vs_golden(golden, name):
+    """float32 exp / pow are SIMD library calls (last bit host-dependent): 1e-6, and the `np.where(unc > 0.5)` choice
+    is compared outside the |unc - 0.5| <= 1e-6 band."""
+    g = golden(name)
+    o = po.fuse_uncertainty(g["in_cond_ori"], g["in_gs"], g["in_soft_ori"])
+    assert o["geo_inten_uncertainty"].dtype == np.float64 and o["masks"].dtype == np.float32
+    assert np.max(np.abs(o["geo_inten_uncertainty"] - g["out_geo_inten_uncertainty"])) <= 1e-6
+    assert np.max(np.abs(o["masks"] - g["out_masks"])) <= 1e-6
+    band = np.abs(g["out_geo_inten_uncertainty"] - 0.5) <= 1e-6
+    same = (o["cond_image"] == g["out_cond_image"]) | band
+    assert same.all()
+
+
+def test_fusion_fixture_set_present():
+    assert len(FUSION) == 3
