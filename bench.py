@@ -103,6 +103,37 @@ def cpu_baseline_sample(tr, ps, pt, seconds):
                       f"oracle/syn3r_oracle.c single thread; target-view rate = pair rate / {pairs_per_view:g}"}
 
 
+def parity_gates(tr, ps, pt, tw, n_pairs=3):
+    """SURVEY 8d 'parity gates reported with every timing': the plan's device outputs of the timed workload against
+    the oracle on a few pairs at full size (first, middle, last)."""
+    import torch
+    from oracle import cpu_oracle as orc
+    S, T, H, W = tr.shape
+    t_ = torch.from_numpy
+    sel = sorted({0, len(ps) // 2, len(ps) - 1})[:n_pairs]
+    g = {"pairs_checked": [int(p) for p in sel], "hole_mask_xor": 0, "winner_mismatch": 0, "colour_max_abs_01": 0.0,
+         "mask_reproj_xor": 0, "soft_mask_max_abs": 0.0}
+    for p in sel:
+        s, t = int(ps[p]), int(pt[p])
+        with np.errstate(all="ignore"):
+            r = orc.forward_warp_ext([tr.rgb[s]], [None], [tr.depth[s]], [tr.pose_src[s]], tr.pose_tgt[t], [tr.K], None)
+            iw = orc.inverse_warp(t_(np.ascontiguousarray(np.moveaxis(tr.rgb[s], -1, 0))), t_(tr.depth[s][None]),
+                                  t_(tr.depth_tgt[t][None]), t_(tr.pose_src[s]), t_(tr.pose_tgt[t]),
+                                  t_(tr.K.astype(np.float32)))
+        g["hole_mask_xor"] += int(np.count_nonzero(tw.out_fwd["mask"][p].cpu().numpy().astype(bool) ^ r["mask"]))
+        win = np.where(r["winner"] >= 0, r["winner"] + s * H * W, -1)
+        g["winner_mismatch"] += int(np.count_nonzero(tw.out_fwd["winner"][p].cpu().numpy() != win))
+        g["colour_max_abs_01"] = max(g["colour_max_abs_01"],
+                                     float(np.max(np.abs(tw.out_fwd["rgb_f32"][p].cpu().numpy() - r["out"]))) / 255.0)
+        g["mask_reproj_xor"] += int(np.count_nonzero(tw.out_inv["mask_reproj"][p].cpu().numpy().astype(bool) ^
+                                                     iw["mask_reproj"].numpy()))
+        a, b = tw.out_inv["soft_mask_reproj"][p].cpu().numpy(), iw["soft_mask_reproj"].numpy()
+        fin = np.isfinite(a) & np.isfinite(b)
+        g["soft_mask_max_abs"] = max(g["soft_mask_max_abs"], float(np.max(np.abs(a[fin] - b[fin]), initial=0)))
+    g["bars"] = "masks and winner: 0 mismatches; colour <= 1e-5 on [0,1]; soft mask <= 2e-6"
+    return g
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU algorithm (oracle port) on all host cores, frames farmed over a
     process pool (frames are independent, SURVEY §8d 'fair multi-core')."""
@@ -410,9 +441,10 @@ def run_ours(args):
                                         "(diffusionGS.py:1572-1597, :1452-1491 on the device)")
             del tw_post
 
-    cpu = None
+    cpu, parity = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline_sample(tr, ps, pt, args.cpu_sample_seconds)
+        parity = parity_gates(tr, ps, pt, tw)
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -421,7 +453,7 @@ def run_ours(args):
                 "config": workload_desc(args, S, T, H, W, len(ps)), "clocks": clocks, "e2e": e2e,
                 "e2e_all_outputs": e2e_all, "e2e_conditioning": e2e_post,
                 "gpu_launches": args.steps * tw.launches_per_run(), "roofline": roofline, "cpu_baseline": cpu,
-                "pair_mpix_per_s": world * args.steps * len(ps) * H * W / 1e6 / (total_ms / 1e3)}
+                "pair_mpix_per_s": world * args.steps * len(ps) * H * W / 1e6 / (total_ms / 1e3), "parity": parity}
         if gather_info is not None:
             line["gather"] = gather_info
         if post is not None:
