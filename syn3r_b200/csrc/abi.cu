@@ -146,14 +146,14 @@ static int launch_tile(const TileArgs &ta, int n_items, cudaStream_t st) {
 }
 
 // fixed-point kernel, then the fp32 kernel over whatever work items it handed back (normally none)
-template <bool WINNER>
-static int launch_tile_fx(const TileArgs &ta, int n_items, cudaStream_t st) {
+template <bool WINNER, bool FLAT>
+static int launch_tile_fx_as(const TileArgs &ta, int n_items, cudaStream_t st) {
     static thread_local int configured_dev = -1;
     const size_t smem = fx_smem_bytes(WINNER), smem_redo = tile_smem_bytes(WINNER);
     int dev = -1;
     SYN3R_TRY_CUDA(cudaGetDevice(&dev));
     if (configured_dev != dev) {
-        SYN3R_TRY_CUDA(cudaFuncSetAttribute(k_fwd_tile_fx<WINNER>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        SYN3R_TRY_CUDA(cudaFuncSetAttribute(k_fwd_tile_fx<WINNER, FLAT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)smem));
         SYN3R_TRY_CUDA(cudaFuncSetAttribute(k_fwd_tile<WINNER, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)smem_redo));
@@ -161,11 +161,17 @@ static int launch_tile_fx(const TileArgs &ta, int n_items, cudaStream_t st) {
     }
     int grid = sm_count();
     if (grid > n_items) grid = n_items;
-    k_fwd_tile_fx<WINNER><<<grid, SYN3R_TILE_THREADS, smem, st>>>(ta);
+    k_fwd_tile_fx<WINNER, FLAT><<<grid, SYN3R_TILE_THREADS, smem, st>>>(ta);
     TileArgs tr = ta;
     tr.redo_mode = 1;
     k_fwd_tile<WINNER, false><<<grid, SYN3R_TILE_THREADS, smem_redo, st>>>(tr);
     return SYN3R_OK;
+}
+// frames of up to SYN3R_FX_FLAT source blocks (1024 x 576 and smaller) take the one-pass cull
+template <bool WINNER>
+static int launch_tile_fx(const TileArgs &ta, int n_items, cudaStream_t st) {
+    return (ta.g.nsb * SYN3R_SB_BLOCKS <= SYN3R_FX_FLAT) ? launch_tile_fx_as<WINNER, true>(ta, n_items, st)
+                                                         : launch_tile_fx_as<WINNER, false>(ta, n_items, st);
 }
 
 }  // namespace syn3r

@@ -38,6 +38,8 @@ namespace syn3r {
 #define SYN3R_FX_UNIT_ROWS 4            /* rows of a source block one warp takes at a time (2 per iteration) */
 #endif
 #define SYN3R_FX_UNITS (SYN3R_BLK_H / SYN3R_FX_UNIT_ROWS)
+#define SYN3R_FX_FLAT (3 * SYN3R_TILE_THREADS)   /* FLAT kernels: frames of up to this many source blocks, culled in one pass;
+                                                   listB holds them all (2304 = a 1024 x 576 frame) */
 #define SYN3R_FX_MAGIC 12582912.0f          /* 1.5 * 2^23: low mantissa bits of (v + MAGIC) are rint(v) */
 #define SYN3R_FX_MAGIC_BITS 0x4B400000
 
@@ -331,14 +333,14 @@ __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__res
 
 __host__ __device__ inline size_t fx_smem_bytes(bool winner) {
     const size_t cells = (size_t)SYN3R_TILE_W * SYN3R_TILE_H;
-    return (cells + SYN3R_TILE_W) * 4 * (winner ? 8 : 6) + (size_t)SYN3R_LOGTAB * 16 + (SYN3R_LISTA + SYN3R_LISTB) * 4 + 64;
+    return (cells + SYN3R_TILE_W) * 4 * (winner ? 8 : 6) + (size_t)SYN3R_LOGTAB * 16 + (SYN3R_LISTA + SYN3R_FX_FLAT) * 4 + 64;
 }
 
 // culls the pair's source blocks against the tile and runs one sweep over the survivors.
 // ctl: [1] nA, [2] nB, [4] / [5] dynamic block counters of sweep 1 / 2, [6] listB is complete and reusable
-template <bool WINNER, int SWEEP>
+template <bool WINNER, int SWEEP, bool FLAT>
 __device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, const FxPairRegs &pr, int p, int s,
-                                        int tx0, int ty0, int tx1, int ty1, bool reuse_list, float cs_inv) {
+                                        int tx0, int ty0, int tx1, int ty1, bool reuse_list, bool fresh, float cs_inv) {
     const TileGeom &g = a.g;
     const int tid = threadIdx.x, lane = tid & 31;
     const int tw = tx1 - tx0 + 1, th = ty1 - ty0 + 1;
@@ -358,8 +360,37 @@ __device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, cons
         run_list(ctl[2]);
         return;
     }
-    const CellBox *sbb = a.sb_box + (size_t)p * g.nsb;
     const CellBox *bbb = a.blk_box + (size_t)p * g.nsb * SYN3R_SB_BLOCKS;
+    if (FLAT) {
+        // small frame (<= SYN3R_FX_FLAT blocks, all of which fit listB): every block box is tested in one pass, one
+        // L2 round trip and one barrier instead of the two-level cull's two and six
+        if (!fresh) {                      // counters left by an earlier pair of this item
+            __syncthreads();
+            if (tid == 0) { ctl[2] = 0; ctl[4] = 0; ctl[5] = 0; }
+            __syncthreads();
+        }
+        const int nblk = g.nsb * SYN3R_SB_BLOCKS;
+        CellBox bx[SYN3R_FX_FLAT / SYN3R_TILE_THREADS];
+#pragma unroll
+        for (int k = 0; k < SYN3R_FX_FLAT / SYN3R_TILE_THREADS; ++k) {
+            const int j = tid + k * SYN3R_TILE_THREADS;
+            bx[k] = (j < nblk) ? bbb[j] : CellBox{1, 1, 0, 0};
+        }
+#pragma unroll
+        for (int k = 0; k < SYN3R_FX_FLAT / SYN3R_TILE_THREADS; ++k) {
+            const int j = tid + k * SYN3R_TILE_THREADS;
+            if (box_hits(bx[k], tx0, ty0, tx1, ty1)) {
+                int bx0, by0;
+                block_origin(g, j / SYN3R_SB_BLOCKS, j % SYN3R_SB_BLOCKS, bx0, by0);
+                sm.listB[atomicAdd(&ctl[2], 1)] = (by0 << 16) | bx0;
+            }
+        }
+        if (tid == 0 && SWEEP == 1) ctl[6] = 1;                 // read behind the barrier that ends the sweep
+        __syncthreads();
+        run_list(ctl[2]);
+        return;
+    }
+    const CellBox *sbb = a.sb_box + (size_t)p * g.nsb;
     for (int base = 0; base < g.nsb; base += SYN3R_LISTA) {
         __syncthreads();
         if (tid == 0) ctl[1] = 0;
@@ -411,7 +442,7 @@ __device__ __forceinline__ unsigned u8_round(float v) {      // clip + round-hal
     return (unsigned)__float2int_rn(fminf(fmaxf(v, 0.0f), 255.0f));
 }
 
-template <bool WINNER>
+template <bool WINNER, bool FLAT>
 __global__ void __launch_bounds__(SYN3R_TILE_THREADS, 1)
 k_fwd_tile_fx(const TileArgs a) {
     const int CELLS = FX_PLANE, NPL = WINNER ? 8 : 6;          // plane stride incl. the trash row
@@ -419,7 +450,7 @@ k_fwd_tile_fx(const TileArgs a) {
     unsigned char *ptr = reinterpret_cast<unsigned char *>(fx_smem + NPL * CELLS);
     sm.logtab = reinterpret_cast<double2 *>(ptr); ptr += (size_t)SYN3R_LOGTAB * 16;
     sm.listA = reinterpret_cast<int *>(ptr); ptr += SYN3R_LISTA * 4;
-    sm.listB = reinterpret_cast<int *>(ptr); ptr += SYN3R_LISTB * 4;
+    sm.listB = reinterpret_cast<int *>(ptr); ptr += SYN3R_FX_FLAT * 4;
     sm.ctl = reinterpret_cast<int *>(ptr);
     int *ctl = sm.ctl;
 
@@ -493,10 +524,10 @@ k_fwd_tile_fx(const TileArgs a) {
             FxPairRegs pr;
             const int p = slot, s = a.pair_src[p];
             if (load_pair(p, pr)) {                            // (a dead pair leaves the tile empty: mask all false)
-                fx_pair<WINNER, 1>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, cs_inv);
+                fx_pair<WINNER, 1, FLAT>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, true, cs_inv);
                 __syncthreads();
                 scan_crowded();
-                fx_pair<WINNER, 2>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, ctl[6] != 0, cs_inv);
+                fx_pair<WINNER, 2, FLAT>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, FLAT || ctl[6] != 0, false, cs_inv);
             }
             __syncthreads();
         } else {                                               // FUSED mode: every pair of the slot, per sweep
@@ -509,8 +540,8 @@ k_fwd_tile_fx(const TileArgs a) {
                     FxPairRegs pr;
                     const int s = a.pair_src[p];
                     if (!load_pair(p, pr)) { poisoned = true; continue; }   // NaN weights poison cells: fp32 path
-                    if (sweep == 1) fx_pair<WINNER, 1>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, cs_inv);
-                    else fx_pair<WINNER, 2>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, cs_inv);
+                    if (sweep == 1) fx_pair<WINNER, 1, FLAT>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, false, cs_inv);
+                    else fx_pair<WINNER, 2, FLAT>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, false, cs_inv);
                 }
                 __syncthreads();
             }

@@ -220,6 +220,20 @@ def test_crowded_cells_take_redo_path():
         _check_slot(o, p, r)
 
 
+def test_large_frame_takes_two_level_cull():
+    """1088 x 576 = 2880 source-block slots > SYN3R_FX_FLAT (2304): the integer tile kernel is launched without the
+    one-pass cull (abi.cu launch_tile_fx) and goes through the super-block / block lists; pair and fused mode."""
+    tr = synth.make_trajectory(2, 1, 576, 1088, seed=57)
+    ps, pt = synth.all_pairs(2, 1)
+    o = _run_pairs(tr, ps, pt)
+    for p, (s, t) in enumerate(zip(ps, pt)):
+        r = _oracle_pair(tr, [s], t)
+        r["winner"] = np.where(r["winner"] >= 0, r["winner"] + s * 576 * 1088, -1).astype(np.int32)
+        _check_slot(o, p, r)
+    o = _run_pairs(tr, ps, pt, fused=True)
+    _check_slot(o, 0, _oracle_pair(tr, list(ps), 0))
+
+
 def test_gate06_and_smooth_rgb():
     tr = synth.make_trajectory(2, 2, 64, 64, seed=41, smooth_rgb=True)
     ps, pt = synth.all_pairs(2, 2)
