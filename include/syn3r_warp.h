@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SYN3R_ABI_VERSION 8
+#define SYN3R_ABI_VERSION 9
 
 enum {
     SYN3R_OK = 0,
@@ -188,6 +188,18 @@ int syn3r_condition_post_batched(const uint8_t *valid, const uint8_t *img_u8, co
  * Any output may be NULL (not all).  H and W must be multiples of 8. */
 int syn3r_fuse_uncertainty_batched(const float *cond_ori, const float *gs, const float *soft_ori, int N, int H, int W,
                                    float *out_cond, float *out_masks, double *out_unc, void *stream);
+
+/* Nearby-frame consistency (model/diffusionGS.py:1347-1355, the tail of consistency_check_from_nearby_images_bw;
+ * SURVEY 8f rank 2): for target frame n, whose neighbour warps are pairs [pair_first[n], pair_first[n+1]) of one
+ * syn3r_inverse_warp_batched call (bandwidth 10, pairs ordered by target),
+ *   out_unc[n]     = 1 - mean_k soft[k]                                               [N,H,W] f32
+ *   out_int_unc[n] = 1 - exp(-(|mean_k warped[k] - images[n]| * inv_sigma)^3)          [N,H,W] f32, norm over channels
+ * soft [P,H,W] = soft_mask_reproj, warped [P,3,H,W] = warped_img, images [N,3,H,W] f32 (0..255), pair_first [N+1] i32
+ * DEVICE, every frame with at least one pair (the reference raises on an empty torch.stack).  inv_sigma = 1 / 0.1 as
+ * float32 (= 10.0f).  Either output may be NULL. */
+int syn3r_nearby_uncertainty_batched(const float *soft, const float *warped, const float *images, const int *pair_first,
+                                     int N, int H, int W, float inv_sigma, float *out_unc, float *out_int_unc,
+                                     void *stream);
 
 /* Score of a pose candidate (model/diffusionGS.py:759-761): out_mean[p] = mean over the frame of
  * 1 - soft[p] (float32 element arithmetic as in the reference, deterministic fixed-order reduction).  soft [P,H,W] is

@@ -105,3 +105,62 @@ def fuse_uncertainty(cond_ori: np.ndarray, gs: np.ndarray, soft_ori: np.ndarray)
     masks = (tot / 64.0).astype(np.float32)
     cond = np.clip(np.where(unc[..., None] > 0.5, g, c), 0, 1).astype(np.float32)
     return dict(masks=masks, cond_image=cond, geo_inten_uncertainty=unc[..., None])
+
+
+def nearby_uncertainty(soft: np.ndarray, warped: np.ndarray, images_chw: np.ndarray, first: np.ndarray,
+                       sigma: float = 0.1) -> dict:
+    """The tail of consistency_check_from_nearby_images_bw (/root/reference/model/diffusionGS.py:1347-1355) in float32,
+    op by op as torch evaluates it on the CUDA device the reference runs it on:
+      conf = stack(masks).mean(0)            sum in list order, times float32(1 / cnt)                     (:1347)
+      unc  = 1 - conf                                                                                    (:1348)
+      wimg = stack(warps).mean(0)                                                                        (:1350)
+      nrm  = sqrt((d0 d0 + d1 d1) + d2 d2),  d = wimg - image_t                (torch.norm over dim 0)  (:1351)
+      iunc = 1 - exp(-((nrm * float32(1 / 0.1)) ** 3))    tensor / python scalar = multiply by the reciprocal; x ** 3 =
+             x * x * x                                                                                   (:1351-1353)
+    (The CPU build of torch divides instead of multiplying: a last-place difference, inside the test tolerance; the
+    fixtures tests/golden/nearby_*.npz were produced on the CPU.)
+    soft [P,H,W], warped [P,3,H,W], images_chw [N,3,H,W] float32; first [N+1]: frame n owns pairs first[n]:first[n+1]."""
+    f32 = np.float32
+    N = images_chw.shape[0]
+    unc = np.empty(images_chw.shape[:1] + images_chw.shape[2:], f32)
+    iunc = np.empty_like(unc)
+    inv_sigma = f32(1.0) / f32(sigma)
+    for n in range(N):
+        k0, k1 = int(first[n]), int(first[n + 1])
+        if k1 == k0:
+            raise RuntimeError("stack expects a non-empty TensorList")
+        factor = f32(1.0) / f32(k1 - k0)
+        cs, ws = soft[k0].astype(f32), warped[k0].astype(f32)
+        for k in range(k0 + 1, k1):
+            cs = (cs + soft[k]).astype(f32)
+            ws = (ws + warped[k]).astype(f32)
+        unc[n] = f32(1) - (cs * factor).astype(f32)
+        d = ((ws * factor).astype(f32) - images_chw[n]).astype(f32)
+        sq = (d * d).astype(f32)
+        nrm = np.sqrt(((sq[0] + sq[1]).astype(f32) + sq[2]).astype(f32)).astype(f32)
+        t = (nrm * inv_sigma).astype(f32)
+        iunc[n] = f32(1) - np.exp(-((t * t).astype(f32) * t).astype(f32)).astype(f32)
+    return dict(uncertainty=unc, intensity_uncertainty=iunc)
+
+
+def nearby_consistency(K, poses, images, depths, window_radius: int = 1, bandwidth: float = 10.0) -> dict:
+    """consistency_check_from_nearby_images_bw (diffusionGS.py:1300-1361) end to end on the CPU: the oracle's
+    inverse_warp (oracle/cpu_oracle.py) per (neighbour -> frame) pair, then nearby_uncertainty."""
+    import torch
+    from . import cpu_oracle as orc
+    n = len(poses)
+    soft, warped, first = [], [], [0]
+    t_ = lambda a: torch.from_numpy(np.ascontiguousarray(a, np.float32))  # noqa: E731
+    for cur in range(n):
+        for ref in range(cur - window_radius, cur + window_radius + 1):
+            if ref == cur or ref < 0 or ref >= n:
+                continue
+            r = orc.inverse_warp(t_(np.moveaxis(images[ref], -1, 0)), t_(depths[ref][None]), t_(depths[cur][None]),
+                                 t_(poses[ref]), t_(poses[cur]), t_(np.asarray(K, np.float32)), bandwidth=bandwidth)
+            soft.append(r["soft_mask_reproj"].numpy())
+            warped.append(r["warped_img"].numpy())
+        first.append(len(soft))
+    if first[-1] == 0:
+        raise RuntimeError("stack expects a non-empty TensorList")
+    img = np.ascontiguousarray(np.moveaxis(np.asarray(images, np.float32), -1, 1))
+    return nearby_uncertainty(np.stack(soft), np.stack(warped), img, np.asarray(first))

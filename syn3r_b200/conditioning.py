@@ -118,3 +118,69 @@ def fuse_uncertainty_batched(cond_ori: torch.Tensor, gs: torch.Tensor, soft_ori:
                                                torch.cuda.current_stream(cond_ori.device).cuda_stream),
               "syn3r_fuse_uncertainty_batched")
     return {k: o[k] for k in want}
+
+
+def nearby_pairs(n_frames: int, window_radius: int = 1):
+    """(pair_src, pair_tgt, pair_first): the (ref_i -> cur_i) warps of diffusionGS.py:1322-1326 in the reference's loop
+    order, grouped by target; pair_first[n] .. pair_first[n+1] are frame n's pairs."""
+    ps, pt, first = [], [], [0]
+    for cur in range(n_frames):
+        for ref in range(cur - window_radius, cur + window_radius + 1):
+            if ref == cur or ref < 0 or ref >= n_frames:
+                continue
+            ps.append(ref)
+            pt.append(cur)
+        first.append(len(ps))
+    return np.asarray(ps, np.int32), np.asarray(pt, np.int32), np.asarray(first, np.int32)
+
+
+def nearby_uncertainty_batched(soft: torch.Tensor, warped: torch.Tensor, images_chw: torch.Tensor,
+                               pair_first: torch.Tensor, *, sigma: float = 0.1,
+                               out: Optional[Dict[str, torch.Tensor]] = None) -> Dict[str, torch.Tensor]:
+    """The tail of consistency_check_from_nearby_images_bw (diffusionGS.py:1347-1355) for all frames in one launch.
+    soft [P,H,W], warped [P,3,H,W] (inverse_warp_batched outputs), images_chw [N,3,H,W] f32, pair_first [N+1] i32: CUDA
+    tensors.  Returns uncertainty [N,H,W] f32 (= 1 - mean soft) and intensity_uncertainty [N,H,W] f32."""
+    L = nat.lib()
+    N, three, H, W = images_chw.shape
+    P = soft.shape[0]
+    assert three == 3 and soft.shape == (P, H, W) and warped.shape == (P, 3, H, W) and pair_first.shape == (N + 1,)
+    assert soft.dtype == warped.dtype == images_chw.dtype == torch.float32 and pair_first.dtype == torch.int32
+    assert soft.is_contiguous() and warped.is_contiguous() and images_chw.is_contiguous()
+    o = dict(out or {})
+    for k in ("uncertainty", "intensity_uncertainty"):
+        if o.get(k) is None:
+            o[k] = torch.empty((N, H, W), dtype=torch.float32, device=soft.device)
+        assert o[k].shape == (N, H, W) and o[k].dtype == torch.float32 and o[k].is_contiguous()
+    inv_sigma = float(np.float32(1.0) / np.float32(sigma))     # tensor / python scalar on CUDA: * (1.0f / 0.1f)
+    nat.check(L.syn3r_nearby_uncertainty_batched(nat.ptr(soft), nat.ptr(warped), nat.ptr(images_chw), nat.ptr(pair_first),
+                                                 N, H, W, inv_sigma, nat.ptr(o["uncertainty"]),
+                                                 nat.ptr(o["intensity_uncertainty"]),
+                                                 torch.cuda.current_stream(soft.device).cuda_stream),
+              "syn3r_nearby_uncertainty_batched")
+    return {k: o[k] for k in ("uncertainty", "intensity_uncertainty")}
+
+
+def consistency_check_from_nearby_images_bw(intrinsics, interpolated_poses, images, depths, *, window_radius: int = 1,
+                                            bandwidth: float = 10.0, device=None):
+    """Drop-in for diffusionGS.py:1300-1361: every frame is warped backward from its neighbours within the window
+    (inverse_warp, bandwidth 10) and the soft reprojection masks / warped colours are averaged.  2 (N-1) warps and
+    the fusion run as two launches instead of the reference's per-pair Python loop.
+    interpolated_poses: N w2c 4x4; images: N (H,W,3) in [0,255]; depths: N (H,W).  Returns the reference's two lists
+    as tensors: uncertainty_masks [N,H,W] f32, intensity_uncertainty_masks [N,H,W] f32 (CUDA)."""
+    from . import warp as w
+    dev = torch.device(device or "cuda")
+    poses = np.stack([np.asarray(p, np.float32) for p in interpolated_poses])
+    n = poses.shape[0]
+    ps, pt, first = nearby_pairs(n, window_radius)
+    if np.any(first[1:] == first[:-1]):
+        raise RuntimeError("a frame without a neighbour: the reference's torch.stack(masks) raises on an empty list "
+                           "(diffusionGS.py:1347)")
+    up = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a), dtype=dt).to(dev)  # noqa: E731
+    img = up(np.stack([np.asarray(i, np.float32) for i in images]), torch.float32).permute(0, 3, 1, 2).contiguous()
+    dep = up(np.stack([np.asarray(d, np.float32) for d in depths]), torch.float32)
+    o = w.inverse_warp_batched(img, dep, dep, np.asarray(intrinsics, np.float32), up(w.inverse_pair_params(poses, poses, ps, pt),
+                                                                                   torch.float32),
+                               up(ps, torch.int32), up(pt, torch.int32), bandwidth=bandwidth,
+                               want=("warped_img", "soft_mask_reproj"))
+    f = nearby_uncertainty_batched(o["soft_mask_reproj"], o["warped_img"], img, up(first, torch.int32))
+    return f["uncertainty"], f["intensity_uncertainty"]

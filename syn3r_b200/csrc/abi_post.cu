@@ -37,6 +37,26 @@ int syn3r_fuse_uncertainty_batched(const float *cond_ori, const float *gs, const
     return check_cuda(cudaGetLastError(), "k_fuse_uncertainty");
 }
 
+int syn3r_nearby_uncertainty_batched(const float *soft, const float *warped, const float *images, const int *pair_first,
+                                     int N, int H, int W, float inv_sigma, float *out_unc, float *out_int_unc,
+                                     void *stream) {
+    if (N == 0) return SYN3R_OK;
+    SYN3R_REQUIRE(soft && warped && images && pair_first, "null required pointer");
+    SYN3R_REQUIRE(N > 0 && N <= 65535 && H > 0 && W > 0, "bad sizes");
+    SYN3R_REQUIRE(out_unc || out_int_unc, "no output requested");
+    const size_t hw = (size_t)H * W;
+    const bool vec = hw % 4 == 0 && (((uintptr_t)soft | (uintptr_t)warped | (uintptr_t)images | (uintptr_t)out_unc |
+                                      (uintptr_t)out_int_unc) & 15) == 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (vec)
+        k_nearby_uncertainty<4><<<dim3((unsigned)((hw / 4 + 255) / 256), N), 256, 0, st>>>(soft, warped, images, pair_first, hw,
+                                                                                       inv_sigma, out_unc, out_int_unc);
+    else
+        k_nearby_uncertainty<1><<<dim3((unsigned)((hw + 255) / 256), N), 256, 0, st>>>(soft, warped, images, pair_first, hw,
+                                                                                   inv_sigma, out_unc, out_int_unc);
+    return check_cuda(cudaGetLastError(), "k_nearby_uncertainty");
+}
+
 size_t syn3r_mean_uncertainty_workspace_bytes(int P) { return P > 0 ? (size_t)P * SYN3R_SC_BLOCKS * sizeof(double) : 0; }
 
 int syn3r_mean_uncertainty_batched(const float *soft, int P, int H, int W, float *out_mean, void *workspace,

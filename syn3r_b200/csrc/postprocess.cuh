@@ -276,4 +276,71 @@ k_fuse_uncertainty(const float *__restrict__ cond_ori, const float *__restrict__
     if (live && out_masks && !(t & 3)) out_masks[((size_t)n * (H / 8) + y0 / 8) * (W / 8) + x / 8] = (float)(all8 / 64.0);
 }
 
+// ---------------------------------------------------------------------------------------------
+// k_nearby_uncertainty: the tail of consistency_check_from_nearby_images_bw (model/diffusionGS.py:1347-1355),
+// one thread per VEC consecutive pixels of a target frame n whose neighbour warps are pairs [first[n], first[n+1]):
+//   conf      = mean_k soft[k]                       (:1347  torch.stack(masks).mean(dim=0): sum in order, * 1/cnt)
+//   out_unc   = 1 - conf                             (:1348)
+//   w_c       = mean_k warped[k][c]                  (:1350)
+//   d         = sqrt((d0^2 + d1^2) + d2^2), d_c = w_c - image[n][c]      (:1351  torch.norm(.., dim=0))
+//   out_int   = 1 - exp(-(d * inv_sigma)^3)          (:1351-1353; a tensor divided by a Python scalar is a multiply
+//               by 1.0f / 0.1f on the CUDA device the reference runs this on, x ** 3 is x * x * x)
+// HBM-bound: (16 cnt + 12) bytes read and 8 written per pixel, every byte once.
+// ---------------------------------------------------------------------------------------------
+template <int VEC>
+struct NbVec { float v[VEC]; };
+template <int VEC>
+__device__ __forceinline__ NbVec<VEC> nb_load(const float *p) {
+    NbVec<VEC> r;
+    if (VEC == 4) { const float4 t = __ldcs(reinterpret_cast<const float4 *>(p)); r.v[0] = t.x; r.v[1] = t.y; r.v[2] = t.z; r.v[VEC - 1] = t.w; }
+    else r.v[0] = __ldcs(p);
+    return r;
+}
+template <int VEC>
+__device__ __forceinline__ void nb_store(float *p, const NbVec<VEC> &r) {
+    if (VEC == 4) __stcs(reinterpret_cast<float4 *>(p), make_float4(r.v[0], r.v[1], r.v[2], r.v[VEC - 1]));
+    else __stcs(p, r.v[0]);
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(256)
+k_nearby_uncertainty(const float *__restrict__ soft, const float *__restrict__ warped, const float *__restrict__ images,
+                     const int *__restrict__ first, size_t hw, float inv_sigma, float *__restrict__ out_unc,
+                     float *__restrict__ out_int) {
+    const int n = blockIdx.y;
+    const size_t i = ((size_t)blockIdx.x * 256 + threadIdx.x) * VEC;
+    if (i >= hw) return;
+    const int k0 = __ldg(first + n), k1 = __ldg(first + n + 1);
+    const float factor = __fdiv_rn(1.0f, (float)(k1 - k0));
+    NbVec<VEC> cs, w0, w1, w2;
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) cs.v[j] = w0.v[j] = w1.v[j] = w2.v[j] = 0.0f;
+    for (int k = k0; k < k1; ++k) {
+        const NbVec<VEC> a = nb_load<VEC>(soft + (size_t)k * hw + i);
+        const float *wp = warped + (size_t)k * 3 * hw + i;
+        const NbVec<VEC> b0 = nb_load<VEC>(wp), b1 = nb_load<VEC>(wp + hw), b2 = nb_load<VEC>(wp + 2 * hw);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            cs.v[j] = (k == k0) ? a.v[j] : __fadd_rn(cs.v[j], a.v[j]);       // NaN and -0 of the first term survive
+            w0.v[j] = (k == k0) ? b0.v[j] : __fadd_rn(w0.v[j], b0.v[j]);
+            w1.v[j] = (k == k0) ? b1.v[j] : __fadd_rn(w1.v[j], b1.v[j]);
+            w2.v[j] = (k == k0) ? b2.v[j] : __fadd_rn(w2.v[j], b2.v[j]);
+        }
+    }
+    const float *ip = images + (size_t)n * 3 * hw + i;
+    const NbVec<VEC> t0 = nb_load<VEC>(ip), t1 = nb_load<VEC>(ip + hw), t2 = nb_load<VEC>(ip + 2 * hw);
+    NbVec<VEC> u, v;
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        u.v[j] = __fsub_rn(1.0f, __fmul_rn(cs.v[j], factor));
+        const float d0 = __fsub_rn(__fmul_rn(w0.v[j], factor), t0.v[j]), d1 = __fsub_rn(__fmul_rn(w1.v[j], factor), t1.v[j]),
+                    d2 = __fsub_rn(__fmul_rn(w2.v[j], factor), t2.v[j]);
+        const float nr = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(d0, d0), __fmul_rn(d1, d1)), __fmul_rn(d2, d2)));
+        const float t = __fmul_rn(nr, inv_sigma);
+        v.v[j] = __fsub_rn(1.0f, expf(-__fmul_rn(__fmul_rn(t, t), t)));
+    }
+    if (out_unc) nb_store<VEC>(out_unc + (size_t)n * hw + i, u);
+    if (out_int) nb_store<VEC>(out_int + (size_t)n * hw + i, v);
+}
+
 }  // namespace syn3r

@@ -147,3 +147,49 @@ def test_fuse_uncertainty_full_size_vs_oracle():
     ci = o["cond_image"].cpu().numpy()
     assert ci.min() >= 0.0 and ci.max() <= 1.0                  # :876
     assert np.all(o["geo_inten_uncertainty"].cpu().numpy()[:, 100:140, 200:330] == 1.0)   # blanked pixels: confidence 0
+
+
+# ---- nearby-frame consistency (diffusionGS.py:1300-1361) ------------------------------------------
+
+@pytest.mark.parametrize("name", ["nearby_0", "nearby_1"])
+def test_nearby_consistency_golden(golden, name):
+    """Drop-in call (two launches: batched inverse warp + fusion) against the reference loop's outputs."""
+    from syn3r_b200 import conditioning as c
+    g = golden(name)
+    unc, iunc = c.consistency_check_from_nearby_images_bw(g["K"], list(g["poses"]), list(g["images"]), list(g["depths"]))
+    assert unc.dtype == torch.float32 and tuple(unc.shape) == g["out_uncertainty"].shape
+    assert np.max(np.abs(unc.cpu().numpy() - g["out_uncertainty"])) <= 2e-6      # soft mask bar (test_gpu_parity)
+    assert np.max(np.abs(iunc.cpu().numpy() - g["out_intensity"])) <= 2e-6
+
+
+def test_nearby_consistency_single_frame_raises(golden):
+    from syn3r_b200 import conditioning as c
+    g = golden("nearby_2")
+    with pytest.raises(RuntimeError):
+        c.consistency_check_from_nearby_images_bw(g["K"], list(g["poses"]), list(g["images"]), list(g["depths"]))
+
+
+@pytest.mark.parametrize("N,H,W,radius", [(5, 40, 64, 1), (4, 33, 47, 2), (2, 576, 1024, 1)])
+def test_nearby_uncertainty_kernel_vs_oracle(N, H, W, radius):
+    """The fusion kernel alone on the oracle's own inputs: 1..2*radius neighbours per frame, odd sizes (scalar path),
+    NaN soft masks (exp of a NaN error) and differences across the whole range of exp(-(d / 0.1)^3)."""
+    from syn3r_b200 import conditioning as c
+    rng = np.random.default_rng(N * 1000 + H)
+    ps, pt, first = c.nearby_pairs(N, radius)
+    P = len(ps)
+    images = (rng.random((N, 3, H, W), dtype=np.float32) * 255).astype(np.float32)
+    warped = (images[pt] + (rng.random((P, 3, H, W), dtype=np.float32) - 0.5) * rng.choice(
+        np.float32([0.0, 0.05, 0.2, 1.0, 50.0]), size=(P, 1, H, W))).astype(np.float32)
+    soft = rng.random((P, H, W), dtype=np.float32)
+    soft[0, ::7, ::5] = np.nan
+    r = po.nearby_uncertainty(soft, warped, images, first)
+    up = lambda a: torch.from_numpy(a).cuda()  # noqa: E731
+    o = c.nearby_uncertainty_batched(up(soft), up(warped), up(images), up(first))
+    torch.cuda.synchronize()
+    assert np.array_equal(o["uncertainty"].cpu().numpy(), r["uncertainty"], equal_nan=True)     # adds and one multiply
+    assert np.max(np.abs(o["intensity_uncertainty"].cpu().numpy() - r["intensity_uncertainty"])) <= 1e-6
+
+
+def test_nearby_uncertainty_empty_is_a_no_op():
+    from syn3r_b200 import _native as nat
+    assert nat.lib().syn3r_nearby_uncertainty_batched(None, None, None, None, 0, 8, 8, 10.0, None, None, None) == 0

@@ -60,3 +60,30 @@ def test_fuse_uncertainty_oracle_vs_golden(golden, name):
 
 def test_fusion_fixture_set_present():
     assert len(FUSION) == 3
+
+
+NEARBY = ["nearby_0", "nearby_1"]
+
+
+@pytest.mark.parametrize("name", NEARBY)
+def test_nearby_consistency_oracle_vs_golden(golden, name):
+    """The oracle chain (cpu_oracle.inverse_warp per neighbour pair + post_oracle.nearby_uncertainty) against the loop
+    of diffusionGS.py:1318-1357 re-executed around the live reference inverse_warp (make_golden_nearby.py).  float32
+    exp is a library call and torch's CPU build divides by 0.1 where its CUDA build multiplies by 10: 1e-6."""
+    g = golden(name)
+    o = po.nearby_consistency(g["K"], g["poses"], g["images"], g["depths"])
+    assert o["uncertainty"].dtype == np.float32 and o["uncertainty"].shape == g["out_uncertainty"].shape
+    assert np.max(np.abs(o["uncertainty"] - g["out_uncertainty"])) <= 1e-6
+    assert np.max(np.abs(o["intensity_uncertainty"] - g["out_intensity"])) <= 1e-6
+    # the steep part of exp(-(d / 0.1)^3) is exercised, not only its saturated ends (first fixture)
+    if name == "nearby_0":
+        mid = (g["out_intensity"] > 0.05) & (g["out_intensity"] < 0.95)
+        assert mid.mean() > 0.1
+
+
+def test_nearby_consistency_single_frame_raises(golden):
+    """One frame has no neighbour: torch.stack([]) raises in the reference (fixture records it), so does the oracle."""
+    g = golden("nearby_2")
+    assert bool(g["raised"])
+    with pytest.raises(RuntimeError):
+        po.nearby_consistency(g["K"], g["poses"], g["images"], g["depths"])
