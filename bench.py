@@ -369,7 +369,26 @@ def run_ours(args):
         t_fu = statistics.mean(timed(fuse, n_k, between=flush.zero_))
         b_fu = Nf * hw * 40 + Nf * (hw // 64) * 4
         del c_ori, g_img, s_ori
-        post = {"kernel": "k_condition_post", "forward_branch_ms": t_fw, "backward_branch_ms": t_bw,
+        # second half of rank 2: nearby-frame consistency of the T interpolated frames (diffusionGS.py:1300-1361):
+        # 2 (T - 1) neighbour warps (batched inverse warp: warped_img + soft mask) and their fusion
+        Nn = max(T, 2)
+        ps_n, pt_n, first_n = conditioning.nearby_pairs(Nn, 1)
+        Pn = len(ps_n)
+        soft_n = torch.rand((Pn, H, W), device=dev)
+        warp_n = torch.rand((Pn, 3, H, W), device=dev) * 255
+        img_n = torch.rand((Nn, 3, H, W), device=dev) * 255
+        first_d = torch.from_numpy(first_n).to(dev)
+        o_nb = {}
+
+        def nearby():
+            o_nb.update(conditioning.nearby_uncertainty_batched(soft_n, warp_n, img_n, first_d, out=o_nb))
+        nearby()
+        t_nb = statistics.mean(timed(nearby, n_k, between=flush.zero_))
+        b_nb = Pn * hw * 16 + Nn * hw * 20                      # soft 4 + warp 12 per pair; image 12 in, 2 x 4 out per frame
+        del soft_n, warp_n, img_n
+        post = {"nearby": {"kernel": "k_nearby_uncertainty", "frames": Nn, "pairs": Pn, "ms": t_nb, "algorithmic_bytes": b_nb,
+                           "achieved_GBps": b_nb / t_nb / 1e6, "frac": b_nb / t_nb / 1e6 / peak},
+                "kernel": "k_condition_post", "forward_branch_ms": t_fw, "backward_branch_ms": t_bw,
                 "fusion": {"kernel": "k_fuse_uncertainty", "frames": Nf, "ms": t_fu, "algorithmic_bytes": b_fu,
                            "achieved_GBps": b_fu / t_fu / 1e6, "frac": b_fu / t_fu / 1e6 / peak},
                 "forward_branch": {"algorithmic_bytes": b_fw, "achieved_GBps": b_fw / t_fw / 1e6, "frac": b_fw / t_fw / 1e6 / peak},
