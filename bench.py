@@ -386,7 +386,28 @@ def run_ours(args):
         t_nb = statistics.mean(timed(nearby, n_k, between=flush.zero_))
         b_nb = Pn * hw * 16 + Nn * hw * 20                      # soft 4 + warp 12 per pair; image 12 in, 2 x 4 out per frame
         del soft_n, warp_n, img_n
-        post = {"nearby": {"kernel": "k_nearby_uncertainty", "frames": Nn, "pairs": Pn, "ms": t_nb, "algorithmic_bytes": b_nb,
+        # rank 4, gmflow half: forward-backward flow consistency of T - 1 frame pairs (geometry.py:75-96)
+        from syn3r_b200 import _native as nat
+        Bf = max(T - 1, 1)
+        yy_, xx_ = torch.meshgrid(torch.arange(H, device=dev, dtype=torch.float32),
+                                  torch.arange(W, device=dev, dtype=torch.float32), indexing="ij")
+        f_fl = torch.stack([2.5 + 3.0 * torch.sin(0.02 * yy_) + 0.01 * xx_, -1.75 + 3.0 * torch.cos(0.015 * xx_) - 0.01 * yy_])
+        f_fl = (f_fl[None] + torch.randn((Bf, 2, H, W), device=dev) * 0.3).contiguous()     # smooth motion + sub-pixel noise
+        b_fl = -f_fl + torch.randn((Bf, 2, H, W), device=dev) * 0.3
+        o_fl = [torch.empty((Bf, H, W), device=dev) for _ in range(2)]
+
+        def flow_fb():
+            nat.check(nat.lib().syn3r_flow_fb_consistency_batched(nat.ptr(f_fl), nat.ptr(b_fl), Bf, H, W, 0.01, 0.5, nat.ptr(o_fl[0]),
+                                                                  nat.ptr(o_fl[1]), None, None,
+                                                                  torch.cuda.current_stream().cuda_stream), "flow_fb")
+        flow_fb()
+        t_fl = statistics.mean(timed(flow_fb, n_k, between=flush.zero_))
+        b_fl_bytes = Bf * hw * 24                               # two 2-channel flows in, two flags out
+        del f_fl, b_fl
+        post = {"flow_fb": {"kernel": "k_flow_fb_consistency", "frame_pairs": Bf, "ms": t_fl, "algorithmic_bytes": b_fl_bytes,
+                            "achieved_GBps": b_fl_bytes / t_fl / 1e6, "frac": b_fl_bytes / t_fl / 1e6 / peak,
+                            "input": "smooth synthetic motion of a few pixels + 0.3 px noise (taps of neighbouring pixels share lines)"},
+                "nearby": {"kernel": "k_nearby_uncertainty", "frames": Nn, "pairs": Pn, "ms": t_nb, "algorithmic_bytes": b_nb,
                            "achieved_GBps": b_nb / t_nb / 1e6, "frac": b_nb / t_nb / 1e6 / peak},
                 "kernel": "k_condition_post", "forward_branch_ms": t_fw, "backward_branch_ms": t_bw,
                 "fusion": {"kernel": "k_fuse_uncertainty", "frames": Nf, "ms": t_fu, "algorithmic_bytes": b_fu,

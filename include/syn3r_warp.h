@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SYN3R_ABI_VERSION 9
+#define SYN3R_ABI_VERSION 10
 
 enum {
     SYN3R_OK = 0,
@@ -200,6 +200,16 @@ int syn3r_fuse_uncertainty_batched(const float *cond_ori, const float *gs, const
 int syn3r_nearby_uncertainty_batched(const float *soft, const float *warped, const float *images, const int *pair_first,
                                      int N, int H, int W, float inv_sigma, float *out_unc, float *out_int_unc,
                                      void *stream);
+
+/* Forward-backward flow consistency (thirdparty/gmflow/gmflow/geometry.py:75-96 forward_backward_consistency_check,
+ * with flow_warp :65-72 and bilinear_sample :41-62), both directions in one launch:
+ *   out_fwd_occ = |fwd + grid_sample(bwd, x + fwd)| > alpha (|fwd| + |bwd|) + beta   as float32 0 / 1, [B,H,W]
+ *   out_bwd_occ = |bwd + grid_sample(fwd, x + bwd)| > the same threshold
+ * fwd_flow, bwd_flow [B,2,H,W] f32 (channel 0 = x displacement), device.  out_diff_* [B,H,W] f32 (extension: the
+ * two norms before thresholding).  Any output may be NULL (not all).  H, W >= 2. */
+int syn3r_flow_fb_consistency_batched(const float *fwd_flow, const float *bwd_flow, int B, int H, int W, float alpha,
+                                      float beta, float *out_fwd_occ, float *out_bwd_occ, float *out_diff_fwd,
+                                      float *out_diff_bwd, void *stream);
 
 /* Score of a pose candidate (model/diffusionGS.py:759-761): out_mean[p] = mean over the frame of
  * 1 - soft[p] (float32 element arithmetic as in the reference, deterministic fixed-order reduction).  soft [P,H,W] is

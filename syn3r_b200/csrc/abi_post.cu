@@ -1,6 +1,7 @@
 // abi_post.cu — extern "C" launcher of the warped-frame post-processing (include/syn3r_warp.h).
 #include "postprocess.cuh"
 #include "score.cuh"
+#include "flow.cuh"
 
 using namespace syn3r;
 
@@ -55,6 +56,23 @@ int syn3r_nearby_uncertainty_batched(const float *soft, const float *warped, con
         k_nearby_uncertainty<1><<<dim3((unsigned)((hw + 255) / 256), N), 256, 0, st>>>(soft, warped, images, pair_first, hw,
                                                                                    inv_sigma, out_unc, out_int_unc);
     return check_cuda(cudaGetLastError(), "k_nearby_uncertainty");
+}
+
+int syn3r_flow_fb_consistency_batched(const float *fwd_flow, const float *bwd_flow, int B, int H, int W, float alpha,
+                                      float beta, float *out_fwd_occ, float *out_bwd_occ, float *out_diff_fwd,
+                                      float *out_diff_bwd, void *stream) {
+    if (B == 0) return SYN3R_OK;
+    SYN3R_REQUIRE(fwd_flow && bwd_flow, "null required pointer");
+    SYN3R_REQUIRE(B > 0 && B <= 65535 && H > 1 && W > 1, "bad sizes (H and W must be at least 2: the reference divides by w - 1)");
+    SYN3R_REQUIRE(out_fwd_occ || out_bwd_occ || out_diff_fwd || out_diff_bwd, "no output requested");
+    const size_t hw = (size_t)H * W;
+    SYN3R_REQUIRE(hw < (1ull << 30), "frame too large (32-bit pixel indices)");
+    cudaStream_t st = (cudaStream_t)stream;
+    const float iw = 1.0f / (float)(W - 1), ih = 1.0f / (float)(H - 1);
+    const size_t per_block = 256 * SYN3R_FLOW_PX;
+    k_flow_fb_consistency<<<dim3((unsigned)((hw + per_block - 1) / per_block), B), 256, 0, st>>>(
+        fwd_flow, bwd_flow, H, W, alpha, beta, iw, ih, out_fwd_occ, out_bwd_occ, out_diff_fwd, out_diff_bwd);
+    return check_cuda(cudaGetLastError(), "k_flow_fb_consistency");
 }
 
 size_t syn3r_mean_uncertainty_workspace_bytes(int P) { return P > 0 ? (size_t)P * SYN3R_SC_BLOCKS * sizeof(double) : 0; }
