@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SYN3R_ABI_VERSION 10
+#define SYN3R_ABI_VERSION 11
 
 enum {
     SYN3R_OK = 0,
@@ -210,6 +210,22 @@ int syn3r_nearby_uncertainty_batched(const float *soft, const float *warped, con
 int syn3r_flow_fb_consistency_batched(const float *fwd_flow, const float *bwd_flow, int B, int H, int W, float alpha,
                                       float beta, float *out_fwd_occ, float *out_bwd_occ, float *out_diff_fwd,
                                       float *out_diff_bwd, void *stream);
+
+/* Guided latent replacement of the patched Euler scheduler (thirdparty/diffusers/src/diffusers/schedulers/
+ * scheduling_euler_discrete.py:1442-1499, also :548-594 and :735-779), all frames in one launch, in
+ * place on pred [b,F,c,h,w] f32 (pred_original_sample):
+ *   for tau in [tau0, tau0 + n_tau) (the reference's index_list 1..23; frames 0 and F - 1 are skipped, see below):
+ *     m_ = channel mean of ((1 - mask) > 0.5), m = m_ > 0.5, d = |pred[:,tau] m - cond[tau] m|,
+ *     k = int(clamp(lambda_row[tau], 0.4, 1) * (b c h w - count(~m))) + count(~m), cutoff = k-th smallest d
+ *     (the reference's torch.sort + index; a radix select here), w = x / (1 + x) with x = 1 / (1 - m_ + 1e-6),
+ *     zeroed below 0.51 and where d > cutoff; pred[:,tau] = (1 - w) pred[:,tau] + w cond[tau];
+ *   pred[:,0] = cond[0], pred[:,F-1] = cond[F-1] (:1496-1499).
+ * cond_latents [F,c,h,w] = temp_cond_latents[1]; mask [mask_batch, F-1, mask_channels, h, w] f32, 1 = hole, as the
+ * pipeline passes it (the scheduler prepends the frame of ones itself); lambda_row [F] = lambda_ts[step_index].  All
+ * device pointers.  out_cutoff_index / out_cutoff_value [n_tau] optional (cutoff_index_e, cutoff_value). */
+int syn3r_latent_guided_replace(float *pred, const float *cond_latents, const float *mask, const float *lambda_row, int b,
+                                int F, int c, int h, int w, int mask_batch, int mask_channels, int tau0, int n_tau,
+                                int *out_cutoff_index, float *out_cutoff_value, void *stream);
 
 /* Score of a pose candidate (model/diffusionGS.py:759-761): out_mean[p] = mean over the frame of
  * 1 - soft[p] (float32 element arithmetic as in the reference, deterministic fixed-order reduction).  soft [P,H,W] is

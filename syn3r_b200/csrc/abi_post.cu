@@ -2,6 +2,7 @@
 #include "postprocess.cuh"
 #include "score.cuh"
 #include "flow.cuh"
+#include "latent.cuh"
 
 using namespace syn3r;
 
@@ -73,6 +74,22 @@ int syn3r_flow_fb_consistency_batched(const float *fwd_flow, const float *bwd_fl
     k_flow_fb_consistency<<<dim3((unsigned)((hw + per_block - 1) / per_block), B), 256, 0, st>>>(
         fwd_flow, bwd_flow, H, W, alpha, beta, iw, ih, out_fwd_occ, out_bwd_occ, out_diff_fwd, out_diff_bwd);
     return check_cuda(cudaGetLastError(), "k_flow_fb_consistency");
+}
+
+int syn3r_latent_guided_replace(float *pred, const float *cond_latents, const float *mask, const float *lambda_row, int b,
+                                int F, int c, int h, int w, int mask_batch, int mask_channels, int tau0, int n_tau,
+                                int *out_cutoff_index, float *out_cutoff_value, void *stream) {
+    SYN3R_REQUIRE(pred && cond_latents && mask && lambda_row, "null required pointer");
+    SYN3R_REQUIRE(b > 0 && F >= 2 && c > 0 && h > 0 && w > 0 && mask_channels > 0, "bad sizes");
+    SYN3R_REQUIRE(mask_batch == 1 || mask_batch == b, "the mask's batch must be 1 or the latents' batch (broadcast of :1464)");
+    SYN3R_REQUIRE(n_tau >= 0 && tau0 >= 1 && tau0 + n_tau <= F, "frame range outside 1 .. F - 1");
+    SYN3R_REQUIRE((size_t)b * c * h * w < (1ull << 24), "b*c*h*w must stay below 2^24 (float32 count of :1479)");
+    LatentArgs a;
+    a.pred = pred; a.cond = cond_latents; a.mask = mask; a.lambda_row = lambda_row;
+    a.b = b; a.F = F; a.c = c; a.hw = h * w; a.bm = mask_batch; a.cm = mask_channels; a.tau0 = tau0; a.n_tau = n_tau;
+    a.out_k = out_cutoff_index; a.out_cutoff = out_cutoff_value;
+    k_latent_guided_replace<<<n_tau + 2, SYN3R_LAT_THREADS, 0, (cudaStream_t)stream>>>(a);
+    return check_cuda(cudaGetLastError(), "k_latent_guided_replace");
 }
 
 size_t syn3r_mean_uncertainty_workspace_bytes(int P) { return P > 0 ? (size_t)P * SYN3R_SC_BLOCKS * sizeof(double) : 0; }

@@ -1,0 +1,137 @@
+// Guided latent replacement of the patched Euler scheduler, SURVEY 8f rank 4 (scheduler half).
+//
+// Reference: /root/reference/thirdparty/diffusers/src/diffusers/schedulers/scheduling_euler_discrete.py:1442-1499
+// (step_interp_prob_uncertain; the same block is :548-594 and :735-779).  Per conditioning frame tau the reference
+// runs a torch.sort over the b*c*h*w absolute differences between the predicted clean latent and the warped
+// conditioning latent, reads ONE order statistic out of it (the cutoff) and blends; about 25 launches per frame, 23
+// frames, 100 steps, two passes.
+//
+// Here: one CTA per frame, all frames in one launch.  The sort becomes a 4-pass radix SELECT on the float bit
+// patterns (non-negative floats order like their bits, NaN above inf like torch.sort's "NaN last"), with per-warp
+// histograms filled through __match_any_sync (no shared-memory atomics: the top byte of nearly every key is the
+// same).  The differences are recomputed from the two latents in every pass (a frame is 2 x 147 KB: L1 / L2
+// resident), never stored.  Results are bit-identical to the reference: a selection and exact float32 arithmetic.
+#pragma once
+#include "common.cuh"
+
+namespace syn3r {
+
+struct LatentArgs {
+    float *pred;                 // [b, F, c, hw] predicted clean latents, updated in place
+    const float *cond;           // [F, c, hw] = temp_cond_latents[1]
+    const float *mask;           // [bm, F - 1, cm, hw], 1 = hole (frame tau of the reference's mask is row tau - 1 here)
+    const float *lambda_row;     // [F] = lambda_ts[step_index]
+    int b, F, c, hw, bm, cm, tau0, n_tau;
+    int *out_k;                  // [n_tau] cutoff_index_e (optional)
+    float *out_cutoff;           // [n_tau] cutoff_value (optional)
+};
+
+#define SYN3R_LAT_THREADS 1024
+
+__global__ void __launch_bounds__(SYN3R_LAT_THREADS)
+k_latent_guided_replace(const LatentArgs a) {
+    __shared__ unsigned s_hist[SYN3R_LAT_THREADS / 32][256];
+    __shared__ unsigned s_tot[256];
+    __shared__ unsigned s_ctl[4];                              // [0] prefix, [1] rank within the prefix, [2] nz
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int chw = a.c * a.hw;
+    const unsigned n = (unsigned)a.b * (unsigned)chw;
+
+    if ((int)blockIdx.x >= a.n_tau) {                          // :1496-1499: first and last frame = the conditioning latents
+        const int fr = ((int)blockIdx.x == a.n_tau) ? 0 : a.F - 1;
+        for (unsigned e = tid; e < n; e += SYN3R_LAT_THREADS) {
+            const unsigned bi = e / chw, r = e - bi * chw;
+            a.pred[((size_t)bi * a.F + fr) * chw + r] = a.cond[(size_t)fr * chw + r];
+        }
+        return;
+    }
+    const int tau = a.tau0 + blockIdx.x;
+    if (tau <= 0 || tau >= a.F - 1) return;                    // frames the copy above overwrites (:1496-1499)
+
+    const float inv_cm = __fdiv_rn(1.0f, (float)a.cm);
+    // mean over the mask's channels of ((1 - mask) > 0.5) for pixel pix of mask batch item mb (:1447, :1457)
+    auto mean_valid = [&](int mb, int pix) -> float {
+        const float *mp = a.mask + (((size_t)mb * (a.F - 1) + (tau - 1)) * a.cm) * a.hw + pix;
+        float s = 0.0f;
+        for (int ch = 0; ch < a.cm; ++ch) s += (__fsub_rn(1.0f, __ldg(mp + (size_t)ch * a.hw)) > 0.5f) ? 1.0f : 0.0f;
+        return __fmul_rn(s, inv_cm);
+    };
+    // |pred * m - FEA * m| of element e (:1464-1469) and the pixel's mean_valid
+    auto diff_of = [&](unsigned e, float &p, float &f, float &mv) -> float {
+        const unsigned bi = e / chw, r = e - bi * chw, pix = r % a.hw;
+        mv = mean_valid(a.bm == 1 ? 0 : (int)bi, (int)pix);
+        const float m = mv > 0.5f ? 1.0f : 0.0f;
+        p = a.pred[((size_t)bi * a.F + tau) * chw + r];
+        f = __ldg(a.cond + (size_t)tau * chw + r);
+        return fabsf(__fsub_rn(__fmul_rn(p, m), __fmul_rn(f, m)));
+    };
+
+    // ---- num_zero (:1461) ------------------------------------------------------------------------------
+    if (tid < 4) s_ctl[tid] = 0;
+    __syncthreads();
+    {
+        unsigned cnt = 0;
+        for (int e = tid; e < a.bm * a.hw; e += SYN3R_LAT_THREADS) cnt += !(mean_valid(e / a.hw, e % a.hw) > 0.5f);
+        cnt = __reduce_add_sync(0xffffffffu, cnt);
+        if (lane == 0 && cnt) atomicAdd(&s_ctl[2], cnt);
+    }
+    __syncthreads();
+    if (tid == 0) {                                            // :1476-1479
+        const unsigned nz = s_ctl[2];
+        const float wt = fminf(fmaxf(__ldg(a.lambda_row + tau), 0.4f), 1.0f);
+        unsigned k = (unsigned)(int)__fmul_rn(wt, (float)(n - nz)) + nz;
+        if (a.out_k) a.out_k[blockIdx.x] = (int)k;
+        if (k == 0) k = n;                                     // sorted[-1]: Python wraps to the largest
+        s_ctl[1] = k - 1;                                      // zero-based rank
+        s_ctl[0] = 0;
+    }
+    // ---- radix select: the (rank)-th smallest key, 8 bits per pass -------------------------------------
+    unsigned known = 0;                                        // bits of the key fixed so far
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        for (int k = lane; k < 256; k += 32) s_hist[warp][k] = 0;
+        __syncthreads();
+        const unsigned prefix = s_ctl[0];
+        for (unsigned e0 = 0; e0 < n; e0 += SYN3R_LAT_THREADS) {      // whole warps stay in the loop for match_any
+            const unsigned e = e0 + tid;
+            unsigned bin = 256u + lane;                        // no contribution: a value no other lane has
+            if (e < n) {
+                float p, f, mv;
+                const unsigned key = __float_as_uint(diff_of(e, p, f, mv));
+                if ((key & known) == prefix) bin = (key >> shift) & 255u;
+            }
+            const unsigned peers = __match_any_sync(0xffffffffu, bin);
+            if (bin < 256u && lane == __ffs(peers) - 1) s_hist[warp][bin] += __popc(peers);
+        }
+        __syncthreads();
+        if (tid < 256) {
+            unsigned t = 0;
+#pragma unroll 8
+            for (int wv = 0; wv < SYN3R_LAT_THREADS / 32; ++wv) t += s_hist[wv][tid];
+            s_tot[tid] = t;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            unsigned r = s_ctl[1], bin = 0;
+            while (bin < 255u && r >= s_tot[bin]) { r -= s_tot[bin]; ++bin; }
+            s_ctl[1] = r;
+            s_ctl[0] = prefix | (bin << shift);
+        }
+        known |= 255u << shift;
+        __syncthreads();
+    }
+    const float cutoff = __uint_as_float(s_ctl[0]);            // :1480
+    if (tid == 0 && a.out_cutoff) a.out_cutoff[blockIdx.x] = cutoff;
+    // ---- blend (:1487-1493) ----------------------------------------------------------------------------
+    for (unsigned e = tid; e < n; e += SYN3R_LAT_THREADS) {
+        float p, f, mv;
+        const float d = diff_of(e, p, f, mv);
+        const float x = __fdiv_rn(1.0f, __fadd_rn(__fsub_rn(1.0f, mv), 1e-6f));
+        float w = __fdiv_rn(x, __fadd_rn(1.0f, x));
+        w = (w >= 0.51f) ? w : 0.0f;
+        w = __fmul_rn((d <= cutoff) ? 1.0f : 0.0f, w);
+        const unsigned bi = e / chw, r = e - bi * chw;
+        a.pred[((size_t)bi * a.F + tau) * chw + r] = __fadd_rn(__fmul_rn(__fsub_rn(1.0f, w), p), __fmul_rn(w, f));
+    }
+}
+
+}  // namespace syn3r

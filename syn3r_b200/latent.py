@@ -1,0 +1,45 @@
+"""Guided latent replacement of the patched Euler scheduler on the device (scheduler half).
+
+The reference (/root/reference/thirdparty/diffusers/src/diffusers/schedulers/scheduling_euler_discrete.py:1442-1499,
+`step_interp_prob_uncertain`; the same block in `step_single` :548-594 and `step_interp` :735-779) loops over the 23
+conditioning frames with a `torch.sort` and ~25 small launches each, 100 steps x 2 passes per clip.  Here the whole block
+is ONE launch (`k_latent_guided_replace`, csrc/latent.cuh: a radix select per frame instead of the sort) through
+`syn3r_latent_guided_replace`; results are bit-identical.  There is no CPU path.
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from . import _native as nat
+
+
+def guided_replace_(pred_original_sample: torch.Tensor, temp_cond_latents: torch.Tensor, mask: torch.Tensor,
+                    lambda_ts: torch.Tensor, step_index: int, index_list: Optional[Sequence[int]] = None, *,
+                    return_cutoffs: bool = False):
+    """In place on pred_original_sample [b,F,c,h,w] (float32, contiguous, CUDA), like the reference's block.
+    temp_cond_latents [2,F,c,h,w] (batch item 1 is used, :1454), mask [bm,F-1,cm,h,w] with 1 = hole as the pipeline
+    passes it, lambda_ts [steps,F], index_list: the frames to blend (default 1 .. F-2; the reference hard-codes
+    1 .. 23 for F = 25) - a contiguous range.  Returns pred_original_sample (and the cutoff indices / values)."""
+    p = pred_original_sample
+    assert p.is_cuda and p.dtype == torch.float32 and p.is_contiguous() and p.dim() == 5
+    b, F, c, h, w = p.shape
+    assert temp_cond_latents.shape[1:] == (F, c, h, w) and temp_cond_latents.shape[0] >= 2
+    cond = temp_cond_latents[1].to(torch.float32).contiguous()
+    m = mask.to(torch.float32).contiguous()
+    assert m.dim() == 5 and m.shape[1] == F - 1 and m.shape[3:] == (h, w)
+    idx = list(range(1, F - 1)) if index_list is None else [int(i) for i in index_list]
+    assert idx == list(range(idx[0], idx[0] + len(idx))) if idx else True, "index_list must be a contiguous range"
+    row = lambda_ts[step_index].to(device=p.device, dtype=torch.float32).contiguous()
+    assert row.shape == (F,)
+    n_tau = len(idx)
+    ks = torch.empty(max(n_tau, 1), dtype=torch.int32, device=p.device) if return_cutoffs else None
+    cv = torch.empty(max(n_tau, 1), dtype=torch.float32, device=p.device) if return_cutoffs else None
+    nat.check(nat.lib().syn3r_latent_guided_replace(nat.ptr(p), nat.ptr(cond), nat.ptr(m), nat.ptr(row), b, F, c, h, w,
+                                                    m.shape[0], m.shape[2], idx[0] if idx else 1, n_tau,
+                                                    nat.ptr(ks) if return_cutoffs else None,
+                                                    nat.ptr(cv) if return_cutoffs else None,
+                                                    torch.cuda.current_stream(p.device).cuda_stream),
+              "syn3r_latent_guided_replace")
+    return (p, ks[:n_tau], cv[:n_tau]) if return_cutoffs else p
