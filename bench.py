@@ -404,7 +404,32 @@ def run_ours(args):
         t_fl = statistics.mean(timed(flow_fb, n_k, between=flush.zero_))
         b_fl_bytes = Bf * hw * 24                               # two 2-channel flows in, two flags out
         del f_fl, b_fl
-        post = {"flow_fb": {"kernel": "k_flow_fb_consistency", "frame_pairs": Bf, "ms": t_fl, "algorithmic_bytes": b_fl_bytes,
+        # rank 4, scheduler half: guided latent replacement of one diffusion step (scheduling_euler_discrete.py:1442-1499),
+        # 25 frames of 4 x 72 x 128 latents; launch-latency bound (25 CTAs, ~11 MB), reported as time per step
+        from syn3r_b200 import latent as latent_mod
+        Fl, hl, wl = 25, H // 8, W // 8
+        p_l = torch.randn((1, Fl, 4, hl, wl), device=dev)
+        c_l = torch.randn((2, Fl, 4, hl, wl), device=dev)
+        m_l = (torch.rand((1, Fl - 1, 1, hl, wl), device=dev) < 0.3).float()
+        lam_l = torch.rand((100, Fl), device=dev)
+
+        cond_l, row_l, REP = c_l[1].contiguous(), lam_l[7].contiguous(), 10
+
+        def latent_step():      # the C-ABI call itself, REP diffusion steps back to back (a 50 us kernel: one Python-level
+            for _ in range(REP):  # call between two events would time the host, not the device)
+                nat.check(nat.lib().syn3r_latent_guided_replace(nat.ptr(p_l), nat.ptr(cond_l), nat.ptr(m_l), nat.ptr(row_l), 1, Fl, 4,
+                                                                hl, wl, 1, 1, 1, Fl - 2, None, None,
+                                                                torch.cuda.current_stream().cuda_stream), "latent")
+        latent_mod.guided_replace_(p_l, c_l, m_l, lam_l, 7)
+        latent_step()
+        t_lat = statistics.mean(timed(latent_step, n_k, between=flush.zero_)) / REP
+        b_lat = (Fl - 2) * 4 * hl * wl * 4 * 3 + (Fl - 2) * hl * wl * 4 + 2 * 4 * hl * wl * 8
+        post = {"latent_replace": {"kernel": "k_latent_guided_replace", "frames": Fl, "latent": [4, hl, wl], "ms": t_lat,
+                                   "algorithmic_bytes": b_lat, "achieved_GBps": b_lat / t_lat / 1e6,
+                                   "frac": b_lat / t_lat / 1e6 / peak,
+                                   "note": "one CTA per frame (25 CTAs): latency bound by design; the reference issues a torch.sort "
+                                           "and ~25 small launches per frame for the same step; mean of 10 back-to-back steps"},
+                "flow_fb": {"kernel": "k_flow_fb_consistency", "frame_pairs": Bf, "ms": t_fl, "algorithmic_bytes": b_fl_bytes,
                             "achieved_GBps": b_fl_bytes / t_fl / 1e6, "frac": b_fl_bytes / t_fl / 1e6 / peak,
                             "input": "smooth synthetic motion of a few pixels + 0.3 px noise (taps of neighbouring pixels share lines)"},
                 "nearby": {"kernel": "k_nearby_uncertainty", "frames": Nn, "pairs": Pn, "ms": t_nb, "algorithmic_bytes": b_nb,

@@ -88,7 +88,16 @@ int syn3r_latent_guided_replace(float *pred, const float *cond_latents, const fl
     a.pred = pred; a.cond = cond_latents; a.mask = mask; a.lambda_row = lambda_row;
     a.b = b; a.F = F; a.c = c; a.hw = h * w; a.bm = mask_batch; a.cm = mask_channels; a.tau0 = tau0; a.n_tau = n_tau;
     a.out_k = out_cutoff_index; a.out_cutoff = out_cutoff_value;
-    k_latent_guided_replace<<<n_tau + 2, SYN3R_LAT_THREADS, 0, (cudaStream_t)stream>>>(a);
+    const size_t key_bytes = (size_t)b * c * h * w * 4, key_cap = 190 * 1024;   // + 34 KB of histograms <= 227 KB
+    a.cache_keys = key_bytes <= key_cap;
+    static thread_local int configured_dev = -1;
+    int dev = -1;
+    SYN3R_TRY_CUDA(cudaGetDevice(&dev));
+    if (configured_dev != dev) {
+        SYN3R_TRY_CUDA(cudaFuncSetAttribute(k_latent_guided_replace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)key_cap));
+        configured_dev = dev;
+    }
+    k_latent_guided_replace<<<n_tau + 2, SYN3R_LAT_THREADS, a.cache_keys ? key_bytes : 0, (cudaStream_t)stream>>>(a);
     return check_cuda(cudaGetLastError(), "k_latent_guided_replace");
 }
 

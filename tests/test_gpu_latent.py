@@ -34,10 +34,11 @@ def test_guided_replace_golden(golden, name):
 
 
 @pytest.mark.parametrize("b,F,c,h,w,bm,cm", [(1, 25, 4, 72, 128, 1, 1), (2, 7, 4, 20, 36, 2, 3), (1, 5, 1, 3, 5, 1, 1),
-                                             (2, 6, 4, 16, 16, 1, 4)])
+                                             (2, 6, 4, 16, 16, 1, 4), (2, 4, 4, 72, 128, 1, 1)])
 def test_guided_replace_vs_oracle(b, F, c, h, w, bm, cm):
     """Production size (25 frames of 4 x 72 x 128) and odd ones; ties in the differences (quantised latents) so that
-    the k-th smallest sits inside a run of equal keys."""
+    the k-th smallest sits inside a run of equal keys.  The last case (2 x 4 x 72 x 128 keys = 288 KB) does not fit
+    the shared-memory key cache and takes the recompute path."""
     rng = np.random.default_rng(b * 1000 + F * 10 + cm)
     pred = rng.normal(0, 1, (b, F, c, h, w)).astype(np.float32)
     tcl = rng.normal(0, 1, (2, F, c, h, w)).astype(np.float32)
