@@ -34,6 +34,17 @@ __device__ __forceinline__ FlowSample flow_sample(const float *__restrict__ fu, 
     // gives 0 for NaN, which is excluded explicitly (a NaN coordinate fails every float comparison: no tap, output 0)
     const int jx = __float2int_rz(x0), jy = __float2int_rz(y0);
     const bool fin = (ix == ix) && (iy == iy);
+    if (fin && (unsigned)jx < (unsigned)(W - 1) && (unsigned)jy < (unsigned)(H - 1)) {
+        // all four taps inside the frame (everything but a one-pixel border and flows leaving the frame): no bounds
+        // tests, no clamps, two row pointers per plane
+        const float *pu = fu + (jy * W + jx), *pv = fv + (jy * W + jx);
+        const float u00 = __ldg(pu), u01 = __ldg(pu + 1), u10 = __ldg(pu + W), u11 = __ldg(pu + W + 1);
+        const float v00 = __ldg(pv), v01 = __ldg(pv + 1), v10 = __ldg(pv + W), v11 = __ldg(pv + W + 1);
+        FlowSample o;
+        o.u = __fmaf_rn(u11, w[3], __fmaf_rn(u10, w[2], __fmaf_rn(u01, w[1], __fmaf_rn(u00, w[0], 0.0f))));
+        o.v = __fmaf_rn(v11, w[3], __fmaf_rn(v10, w[2], __fmaf_rn(v01, w[1], __fmaf_rn(v00, w[0], 0.0f))));
+        return o;
+    }
     const bool okx[2] = {(unsigned)jx < (unsigned)W, (unsigned)(jx + 1) < (unsigned)W && jx != INT_MAX};
     const bool oky[2] = {fin && (unsigned)jy < (unsigned)H, fin && (unsigned)(jy + 1) < (unsigned)H && jy != INT_MAX};
     // the four taps are loaded unconditionally from clamped addresses (so that all loads of a thread are in flight
