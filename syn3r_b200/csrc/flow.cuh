@@ -75,8 +75,13 @@ __device__ __forceinline__ float flow_norm(float a, float b) {
 // A warp owns 32 * SYN3R_FLOW_PX consecutive pixels; lane l takes pixels l, l + 32, l + 64, ...: every load and store
 // instruction of the warp covers 32 consecutive pixels (coalesced, taps included when the motion is smooth), and a
 // thread has 4 + 16 loads per pixel in flight for SYN3R_FLOW_PX pixels.
+#ifndef SYN3R_FLOW_PX
 #define SYN3R_FLOW_PX 4
-__global__ void __launch_bounds__(256, 4)
+#endif
+#ifndef SYN3R_FLOW_MINB
+#define SYN3R_FLOW_MINB 4
+#endif
+__global__ void __launch_bounds__(256, SYN3R_FLOW_MINB)
 k_flow_fb_consistency(const float *__restrict__ fwd, const float *__restrict__ bwd, int H, int W, float alpha, float beta,
                       float inv_wm1, float inv_hm1, float *__restrict__ o_fwd_occ, float *__restrict__ o_bwd_occ,
                       float *__restrict__ o_diff_fwd, float *__restrict__ o_diff_bwd) {
