@@ -90,3 +90,59 @@ def test_consistency_fuzz_vs_oracle(kind, seed):
         fin = np.isfinite(a) & np.isfinite(b)
         assert np.array_equal(np.isnan(a), np.isnan(b)), (kind, seed, p)
         assert np.max(np.abs(a[fin] - b[fin]), initial=0) <= 2e-6, (kind, seed, p)
+
+
+# ---- §8f rank 4 kernels: random shapes and value ranges against their oracles ------------------------------------
+
+@pytest.mark.parametrize("seed", range(12))
+def test_fuzz_latent_guided_replace(seed):
+    """Random batch / frame / channel / latent sizes, mask layouts, hole fractions from none to all, lambda rows
+    outside the clamp range, duplicated and special values: bit-exact against oracle/latent_oracle.py."""
+    from oracle import latent_oracle as lo
+    from syn3r_b200 import latent
+    rng = np.random.default_rng(9000 + seed)
+    b, F, c = int(rng.integers(1, 3)), int(rng.integers(3, 9)), int(rng.integers(1, 5))
+    h, w = int(rng.integers(1, 24)), int(rng.integers(1, 40))
+    bm = b if rng.random() < 0.5 else 1
+    cm = int(rng.choice([1, 2, 3, 4]))
+    pred = rng.normal(0, rng.choice([1e-3, 1.0, 50.0]), (b, F, c, h, w)).astype(np.float32)
+    tcl = rng.normal(0, 1, (2, F, c, h, w)).astype(np.float32)
+    q = float(rng.choice([0.0, 1 / 8, 1 / 64]))
+    noise = rng.normal(0, 0.3, (F, c, h, w))
+    tcl[1] = (pred[0] + (np.round(noise / q) * q if q else noise)).astype(np.float32)
+    mask = (rng.random((bm, F - 1, cm, h, w)) < rng.choice([0.0, 0.2, 0.7, 1.0])).astype(np.float32)
+    if seed % 4 == 1:
+        pred.ravel()[rng.integers(0, pred.size, 3)] = [np.nan, np.inf, -np.inf]
+    lam = (rng.random((2, F)) * 1.5).astype(np.float32)
+    r = lo.guided_replace(pred, tcl, mask, lam, 1)
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    out, ks, cv = latent.guided_replace_(up(pred.copy()), up(tcl), up(mask), up(lam), 1, return_cutoffs=True)
+    torch.cuda.synchronize()
+    assert np.array_equal(ks.cpu().numpy(), r["cutoff_index"])
+    assert np.array_equal(cv.cpu().numpy(), r["cutoff_value"], equal_nan=True)
+    assert np.array_equal(out.cpu().numpy(), r["out"], equal_nan=True)
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_fuzz_flow_fb_consistency(seed):
+    """Random sizes (odd widths, tiny frames), flow magnitudes from sub-pixel to larger than the frame, thresholds:
+    norms to float32 rounding, flags outside a narrow band around the threshold."""
+    from oracle import flow_oracle as fo
+    from syn3r_b200 import flow
+    rng = np.random.default_rng(9100 + seed)
+    B, H, W = int(rng.integers(1, 4)), int(rng.integers(2, 70)), int(rng.integers(2, 90))
+    amp = float(rng.choice([0.2, 2.0, 15.0, 200.0]))
+    fwd = rng.normal(0, amp, (B, 2, H, W)).astype(np.float32)
+    bwd = (-fwd + rng.normal(0, 0.3, (B, 2, H, W))).astype(np.float32)
+    if seed % 3 == 0:
+        fwd = np.round(fwd).astype(np.float32)            # taps exactly on pixel centres and on the frame border
+    alpha, beta = float(rng.choice([0.01, 0.05, 0.0])), float(rng.choice([0.5, 0.1, 1.0]))
+    r = fo.forward_backward_consistency_check(fwd, bwd, alpha, beta)
+    o = flow.forward_backward_consistency_check(torch.from_numpy(fwd).cuda(), torch.from_numpy(bwd).cuda(), alpha, beta,
+                                                return_diff=True)
+    torch.cuda.synchronize()
+    tol = 2e-6 * max(1.0, amp * 4)
+    for occ, diff, d in ((o[0], o[2], "fwd"), (o[1], o[3], "bwd")):
+        assert np.max(np.abs(diff.cpu().numpy() - r["diff_" + d])) <= tol
+        near = np.abs(r["diff_" + d] - r["threshold"]) <= tol
+        assert ((occ.cpu().numpy() == r[d + "_occ"]) | near).all()
