@@ -38,8 +38,9 @@ namespace syn3r {
 #define SYN3R_FX_UNIT_ROWS 4            /* rows of a source block one warp takes at a time (2 per iteration) */
 #endif
 #define SYN3R_FX_UNITS (SYN3R_BLK_H / SYN3R_FX_UNIT_ROWS)
-#define SYN3R_FX_FLAT (3 * SYN3R_TILE_THREADS)   /* FLAT kernels: frames of up to this many source blocks, culled in one pass;
-                                                   listB holds them all (2304 = a 1024 x 576 frame) */
+#define SYN3R_FX_FLAT 2304    /* FLAT kernels: frames of up to this many source blocks (a 1024 x 576 frame), culled in one
+                                 pass; listB holds them all */
+#define SYN3R_FX_FLAT_PER_THREAD ((SYN3R_FX_FLAT + SYN3R_TILE_THREADS - 1) / SYN3R_TILE_THREADS)
 #define SYN3R_FX_MAGIC 12582912.0f          /* 1.5 * 2^23: low mantissa bits of (v + MAGIC) are rint(v) */
 #define SYN3R_FX_MAGIC_BITS 0x4B400000
 
@@ -370,14 +371,14 @@ __device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, cons
             __syncthreads();
         }
         const int nblk = g.nsb * SYN3R_SB_BLOCKS;
-        CellBox bx[SYN3R_FX_FLAT / SYN3R_TILE_THREADS];
+        CellBox bx[SYN3R_FX_FLAT_PER_THREAD];
 #pragma unroll
-        for (int k = 0; k < SYN3R_FX_FLAT / SYN3R_TILE_THREADS; ++k) {
+        for (int k = 0; k < SYN3R_FX_FLAT_PER_THREAD; ++k) {
             const int j = tid + k * SYN3R_TILE_THREADS;
             bx[k] = (j < nblk) ? bbb[j] : CellBox{1, 1, 0, 0};
         }
 #pragma unroll
-        for (int k = 0; k < SYN3R_FX_FLAT / SYN3R_TILE_THREADS; ++k) {
+        for (int k = 0; k < SYN3R_FX_FLAT_PER_THREAD; ++k) {
             const int j = tid + k * SYN3R_TILE_THREADS;
             if (box_hits(bx[k], tx0, ty0, tx1, ty1)) {
                 int bx0, by0;
