@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SYN3R_ABI_VERSION 11
+#define SYN3R_ABI_VERSION 12
 
 enum {
     SYN3R_OK = 0,
@@ -212,7 +212,7 @@ int syn3r_flow_fb_consistency_batched(const float *fwd_flow, const float *bwd_fl
                                       float *out_diff_bwd, void *stream);
 
 /* Guided latent replacement of the patched Euler scheduler (thirdparty/diffusers/src/diffusers/schedulers/
- * scheduling_euler_discrete.py:1442-1499, also :548-594 and :735-779), all frames in one launch, in
+ * scheduling_euler_discrete.py:1442-1499, step_interp_prob_uncertain), all frames in one launch, in
  * place on pred [b,F,c,h,w] f32 (pred_original_sample):
  *   for tau in [tau0, tau0 + n_tau) (the reference's index_list 1..23; frames 0 and F - 1 are skipped, see below):
  *     m_ = channel mean of ((1 - mask) > 0.5), m = m_ > 0.5, d = |pred[:,tau] m - cond[tau] m|,
@@ -226,6 +226,16 @@ int syn3r_flow_fb_consistency_batched(const float *fwd_flow, const float *bwd_fl
 int syn3r_latent_guided_replace(float *pred, const float *cond_latents, const float *mask, const float *lambda_row, int b,
                                 int F, int c, int h, int w, int mask_batch, int mask_channels, int tau0, int n_tau,
                                 int *out_cutoff_index, float *out_cutoff_value, void *stream);
+
+/* The selection half of the same block as step_single (:548-586) and step_interp (:735-774) use it: identical mask
+ * binarisation, sort and cutoff, with the caller's weight_clamp as the lower clamp of lambda (:577, :766) and the
+ * boolean top_mask = (d <= cutoff) & m kept instead of a blend (:583, :772).  pred is only read; tau may reach F - 1
+ * (their index_list runs to 24).  out_top_masks [n_tau, b, c, h, w] u8 0 / 1 (the reference concatenates the frames
+ * and prepends a frame of ones, :586-589). */
+int syn3r_latent_top_masks(const float *pred, const float *cond_latents, const float *mask, const float *lambda_row, int b,
+                           int F, int c, int h, int w, int mask_batch, int mask_channels, int tau0, int n_tau,
+                           float weight_clamp, uint8_t *out_top_masks, int *out_cutoff_index, float *out_cutoff_value,
+                           void *stream);
 
 /* Score of a pose candidate (model/diffusionGS.py:759-761): out_mean[p] = mean over the frame of
  * 1 - soft[p] (float32 element arithmetic as in the reference, deterministic fixed-order reduction).  soft [P,H,W] is

@@ -3,7 +3,8 @@
 TEST INFRASTRUCTURE ONLY: imported by tests/ as the checker, never by the product (syn3r_b200/ has no CPU path).
 
 Follows /root/reference/thirdparty/diffusers/src/diffusers/schedulers/scheduling_euler_discrete.py:1442-1499
-(`step_interp_prob_uncertain`; the same block is :548-594 `step_single` and :735-779 `step_interp`) in float32 NumPy:
+(`step_interp_prob_uncertain`) in float32 NumPy; `top_masks` restates the selection-only form of `step_single` (:548-589)
+and `step_interp` (:735-778), which clamp lambda at the caller's `weight_clamp` and keep the boolean mask:
 
   valid    = (1 - mask) > 0.5, a frame of ones prepended                                     (:1447-1451)
   per frame tau of index_list:
@@ -57,3 +58,36 @@ def guided_replace(pred: np.ndarray, temp_cond_latents: np.ndarray, mask: np.nda
     pred[:, 0:1] = temp_cond_latents[1:2, 0:1]
     pred[:, -1:] = temp_cond_latents[1:2, -1:]
     return dict(out=pred, cutoff_index=np.array(ks), cutoff_value=np.array(cuts, f32))
+
+
+def top_masks(pred: np.ndarray, temp_cond_latents: np.ndarray, mask: np.ndarray, lambda_ts: np.ndarray, step_index: int,
+              weight_clamp: float, index_list=None) -> dict:
+    """scheduling_euler_discrete.py:548-589 (`step_single`; `step_interp` :735-778 is the same with index_list to 23):
+    the selection of guided_replace with `torch.clamp(weight, weight_clamp, 1)` (:577), no blend; top_masks is the
+    reference's [1, 1 + len(index_list) * b, c, h, w] bool tensor (frames concatenated on dim 0, unsqueezed, a frame
+    of ones prepended, :586-589)."""
+    pred = pred.astype(f32)
+    b, F, c, h, w = pred.shape
+    index_list = list(range(1, F)) if index_list is None else list(index_list)
+    valid = (f32(1) - mask.astype(f32)) > f32(0.5)
+    valid = np.concatenate([np.ones_like(valid[:, :1]), valid], axis=1)
+    tops, ks, cuts = [], [], []
+    with np.errstate(invalid="ignore", over="ignore"):
+        for tau in index_list:
+            fea = temp_cond_latents[1:2, tau].astype(f32)
+            cm = valid.shape[2]
+            m_ = (valid[:, tau].astype(f32).sum(axis=1, keepdims=True, dtype=f32) * (f32(1) / f32(cm))).astype(f32)
+            m = m_ > f32(0.5)
+            nz = int((~m).sum())
+            mf = m.astype(f32)
+            d = np.abs(((pred[:, tau] * mf).astype(f32) - (fea * mf).astype(f32)).astype(f32))
+            flat = np.sort(d.ravel())
+            wt = f32(min(max(f32(lambda_ts[step_index, tau]), f32(weight_clamp)), f32(1)))
+            k = int(f32(wt * f32(flat.size - nz))) + nz
+            cutoff = flat[k - 1]
+            tops.append((d <= cutoff) & m)
+            ks.append(k)
+            cuts.append(cutoff)
+    t = np.concatenate(tops, axis=0)[None]
+    t = np.concatenate([np.ones_like(t[:, :1]), t], axis=1)
+    return dict(top_masks=t, cutoff_index=np.array(ks), cutoff_value=np.array(cuts, f32))

@@ -1,7 +1,8 @@
 // Guided latent replacement of the patched Euler scheduler, SURVEY 8f rank 4 (scheduler half).
 //
 // Reference: /root/reference/thirdparty/diffusers/src/diffusers/schedulers/scheduling_euler_discrete.py:1442-1499
-// (step_interp_prob_uncertain; the same block is :548-594 and :735-779).  Per conditioning frame tau the reference
+// (step_interp_prob_uncertain).  step_single (:548-586) and step_interp (:735-774) share the selection (mask, sort,
+// cutoff) with a caller-given lower clamp and keep the boolean top_mask instead of blending: `blend = 0`.  Per conditioning frame tau the reference
 // runs a torch.sort over the b*c*h*w absolute differences between the predicted clean latent and the warped
 // conditioning latent, reads ONE order statistic out of it (the cutoff) and blends; about 25 launches per frame, 23
 // frames, 100 steps, two passes.
@@ -24,6 +25,9 @@ struct LatentArgs {
     const float *mask;           // [bm, F - 1, cm, hw], 1 = hole (frame tau of the reference's mask is row tau - 1 here)
     const float *lambda_row;     // [F] = lambda_ts[step_index]
     int b, F, c, hw, bm, cm, tau0, n_tau;
+    float clamp_lo;              // lower clamp of lambda: 0.4 (:1476) or the caller's weight_clamp (:577, :766)
+    int blend;                   // 1: the soft blend of :1487-1499 in place; 0: selection only (pred is not written)
+    unsigned char *out_top;      // [n_tau, b, c, hw] top_mask = (d <= cutoff) & m (:583, :772, :1483), optional
     int cache_keys;              // 1: the frame's b*c*hw keys fit the dynamic shared memory and are staged there once
     int *out_k;                  // [n_tau] cutoff_index_e (optional)
     float *out_cutoff;           // [n_tau] cutoff_value (optional)
@@ -41,7 +45,7 @@ k_latent_guided_replace(const LatentArgs a) {
     const int chw = a.c * a.hw;
     const unsigned n = (unsigned)a.b * (unsigned)chw;
 
-    if ((int)blockIdx.x >= a.n_tau) {                          // :1496-1499: first and last frame = the conditioning latents
+    if ((int)blockIdx.x >= a.n_tau) {                          // (launched only when blending) :1496-1499: first and last frame = the conditioning latents
         const int fr = ((int)blockIdx.x == a.n_tau) ? 0 : a.F - 1;
         for (unsigned e = tid; e < n; e += SYN3R_LAT_THREADS) {
             const unsigned bi = e / chw, r = e - bi * chw;
@@ -50,7 +54,7 @@ k_latent_guided_replace(const LatentArgs a) {
         return;
     }
     const int tau = a.tau0 + blockIdx.x;
-    if (tau <= 0 || tau >= a.F - 1) return;                    // frames the copy above overwrites (:1496-1499)
+    if (tau <= 0 || tau >= a.F - (a.blend ? 1 : 0)) return;    // blending: frame F - 1 is overwritten by the copy above
 
     const float inv_cm = __fdiv_rn(1.0f, (float)a.cm);
     // mean over the mask's channels of ((1 - mask) > 0.5) for pixel pix of mask batch item mb (:1447, :1457)
@@ -83,7 +87,7 @@ k_latent_guided_replace(const LatentArgs a) {
     __syncthreads();
     if (tid == 0) {                                            // :1476-1479
         const unsigned nz = s_ctl[2];
-        const float wt = fminf(fmaxf(__ldg(a.lambda_row + tau), 0.4f), 1.0f);
+        const float wt = fminf(fmaxf(__ldg(a.lambda_row + tau), a.clamp_lo), 1.0f);
         unsigned k = (unsigned)(int)__fmul_rn(wt, (float)(n - nz)) + nz;
         if (a.out_k) a.out_k[blockIdx.x] = (int)k;
         if (k == 0) k = n;                                     // sorted[-1]: Python wraps to the largest
@@ -153,17 +157,21 @@ k_latent_guided_replace(const LatentArgs a) {
     }
     const float cutoff = __uint_as_float(s_ctl[0]);            // :1480
     if (tid == 0 && a.out_cutoff) a.out_cutoff[blockIdx.x] = cutoff;
-    // ---- blend (:1487-1493) ----------------------------------------------------------------------------
+    // ---- top mask (:1483) and blend (:1487-1493) --------------------------------------------------------
 #pragma unroll 4
     for (unsigned e = tid; e < n; e += SYN3R_LAT_THREADS) {
         float p, f, mv;
         const float d = diff_of(e, p, f, mv);
-        const float x = __fdiv_rn(1.0f, __fadd_rn(__fsub_rn(1.0f, mv), 1e-6f));
-        float w = __fdiv_rn(x, __fadd_rn(1.0f, x));
-        w = (w >= 0.51f) ? w : 0.0f;
-        w = __fmul_rn((d <= cutoff) ? 1.0f : 0.0f, w);
-        const unsigned bi = e / chw, r = e - bi * chw;
-        a.pred[((size_t)bi * a.F + tau) * chw + r] = __fadd_rn(__fmul_rn(__fsub_rn(1.0f, w), p), __fmul_rn(w, f));
+        const bool sel = d <= cutoff;
+        if (a.out_top) a.out_top[(size_t)blockIdx.x * n + e] = sel && (mv > 0.5f);
+        if (a.blend) {
+            const float x = __fdiv_rn(1.0f, __fadd_rn(__fsub_rn(1.0f, mv), 1e-6f));
+            float w = __fdiv_rn(x, __fadd_rn(1.0f, x));
+            w = (w >= 0.51f) ? w : 0.0f;
+            w = __fmul_rn(sel ? 1.0f : 0.0f, w);
+            const unsigned bi = e / chw, r = e - bi * chw;
+            a.pred[((size_t)bi * a.F + tau) * chw + r] = __fadd_rn(__fmul_rn(__fsub_rn(1.0f, w), p), __fmul_rn(w, f));
+        }
     }
 }
 

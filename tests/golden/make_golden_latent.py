@@ -4,7 +4,8 @@ tests/golden/latent_*.npz.
 The patched scheduler (/root/reference/thirdparty/diffusers/src/diffusers/schedulers/scheduling_euler_discrete.py)
 cannot be imported here: the vendored diffusers needs `huggingface_hub.cached_download`, which the installed hub no
 longer has.  The fixture generator therefore RE-EXECUTES the statements of the replacement block (:1442-1499, the
-same block as :548-594 and :735-779) with torch on the CPU, in the reference's order; `self.step_index` becomes an
+soft-blend form of `step_interp_prob_uncertain`) and of the selection-only form of `step_single` (:548-589; `step_interp`
+:735-778 differs only in its index list) with torch on the CPU, in the reference's order; `self.step_index` becomes an
 argument and the hard-coded `index_list = [1..23]` becomes `range(1, F - 1)` (identical for the production F = 25)
 so that short clips can be stored.  Run in the build container:
 
@@ -55,6 +56,41 @@ def reference_replace(pred_original_sample, temp_cond_latents, mask, lambda_ts, 
     return pred_original_sample, aux
 
 
+def reference_top_masks(pred_original_sample, temp_cond_latents, mask, lambda_ts, step_index, weight_clamp):
+    """scheduling_euler_discrete.py:548-589 (`step_single`), statements in the reference's order; index_list
+    [1..24] of the production F = 25 becomes range(1, F)."""
+    b, cond_len, c, h, w = temp_cond_latents.shape
+    index_list = list(range(1, pred_original_sample.shape[1]))
+    mask = (1 - mask) > 0.5
+    mask_ones = torch.ones_like(mask[:, 0:1, :, :, :])
+    mask = torch.cat((mask_ones, mask), 1)
+    top_masks = []
+    aux = []
+    for ii, tau in enumerate(index_list):
+        FEA = temp_cond_latents[1:2, tau, :, :, :]
+        weight = lambda_ts[step_index, tau]
+        mask_t = torch.mean(mask[:, tau, :, :, :].float(), 1, keepdim=True)
+        mask_t = mask_t > 0.5
+        mask_zero = ~mask_t
+        num_zero = torch.sum(mask_zero)
+        masked_tensor1 = pred_original_sample[:, tau, :, :, :] * mask_t
+        masked_tensor2 = FEA * mask_t
+        masked_diff = masked_tensor1 - masked_tensor2
+        flat_diff = torch.abs(masked_diff.flatten())
+        sorted_diff, indices = torch.sort(flat_diff)
+        weight = torch.clamp(weight, weight_clamp, 1)
+        cutoff_index_e = int(weight * (len(sorted_diff) - num_zero)) + num_zero
+        cutoff_value = sorted_diff[cutoff_index_e - 1]
+        top_mask = (torch.abs(masked_diff) <= cutoff_value) & mask_t
+        top_masks.append(top_mask)
+        aux.append((int(cutoff_index_e), float(cutoff_value)))
+    top_masks = torch.cat(top_masks, 0)
+    top_masks = top_masks.unsqueeze(0)
+    mask_ones = torch.ones_like(top_masks[:, 0:1, :, :, :])
+    top_masks = torch.cat((mask_ones, top_masks), 1)
+    return top_masks, aux
+
+
 def main():
     vers = np.array([f"numpy {np.__version__}", f"torch {torch.__version__}",
                      "statements of DecaYale/SYN3R@402f4e9 scheduling_euler_discrete.py:1442-1499"])
@@ -85,6 +121,15 @@ def main():
                             aux_cutoff_index=np.array([a[0] for a in aux]), aux_cutoff_value=np.array([a[1] for a in aux], np.float32))
         print(os.path.basename(path), os.path.getsize(path) // 1024, "KiB", "replaced fraction",
               float((out[:, 1:-1] != pred[:, 1:-1]).float().mean()))
+        if i in (0, 1, 4):
+            wc = [0.5, 0.2, 0.8][(0, 1, 4).index(i)]
+            tm, aux = reference_top_masks(pred.clone(), tcl, mask.clone(), lambda_ts, step, wc)
+            path = os.path.join(HERE, f"latent_top_{i}.npz")
+            np.savez_compressed(path, versions=vers, pred=pred.numpy(), temp_cond_latents=tcl.numpy(), mask=mask.numpy(),
+                                lambda_ts=lambda_ts.numpy(), step_index=np.int64(step), weight_clamp=np.float64(wc),
+                                out_top_masks=tm.numpy(), aux_cutoff_index=np.array([a[0] for a in aux]),
+                                aux_cutoff_value=np.array([a[1] for a in aux], np.float32))
+            print(os.path.basename(path), os.path.getsize(path) // 1024, "KiB", "selected fraction", float(tm.float().mean()))
 
 
 if __name__ == "__main__":

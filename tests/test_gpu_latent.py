@@ -11,7 +11,7 @@ pytestmark = pytest.mark.gpu
 from oracle import latent_oracle as lo  # noqa: E402  (checker only)
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-LATENT = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "latent_*.npz")))
+LATENT = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "latent_[0-9].npz")))
 
 
 def _run(pred, tcl, mask, lam, step, **kw):
@@ -65,3 +65,22 @@ def test_guided_replace_sub_range_and_bad_arguments():
     z = torch.zeros(8, device="cuda")
     assert nat.lib().syn3r_latent_guided_replace(nat.ptr(z), nat.ptr(z), nat.ptr(z), nat.ptr(z), 1, 8, 1, 1, 1, 1, 1, 0, 3,
                                                  None, None, None) != 0            # tau0 = 0 is outside 1 .. F - 1
+
+
+TOP = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "latent_top_*.npz")))
+
+
+@pytest.mark.parametrize("name", TOP)
+def test_top_masks_golden(golden, name):
+    """Selection-only entry point (step_single :548-589): same kernel, blend off, weight_clamp as the lower clamp."""
+    from syn3r_b200 import latent
+    g = golden(name)
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    p = up(g["pred"])
+    tm, ks, cv = latent.top_masks(p, up(g["temp_cond_latents"]), up(g["mask"]), up(g["lambda_ts"]), int(g["step_index"]),
+                                  float(g["weight_clamp"]), return_cutoffs=True)
+    torch.cuda.synchronize()
+    assert tm.dtype == torch.bool and np.array_equal(tm.cpu().numpy(), g["out_top_masks"])
+    assert np.array_equal(ks.cpu().numpy(), g["aux_cutoff_index"])
+    assert np.array_equal(cv.cpu().numpy(), g["aux_cutoff_value"], equal_nan=True)
+    assert np.array_equal(p.cpu().numpy(), g["pred"], equal_nan=True)                 # pred untouched

@@ -8,11 +8,11 @@ import pytest
 from oracle import latent_oracle as lo  # checker only
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-LATENT = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "latent_*.npz")))
+LATENT = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "latent_[0-9].npz")))
 
 
 def test_latent_fixture_set_present():
-    assert len(LATENT) == 5
+    assert len(LATENT) == 5      # latent_[0-4].npz
 
 
 @pytest.mark.parametrize("name", LATENT)
@@ -25,3 +25,20 @@ def test_guided_replace_oracle_vs_golden(golden, name):
     assert np.array_equal(o["cutoff_value"], g["aux_cutoff_value"], equal_nan=True)
     # first and last frame are the conditioning latents (:1496-1499)
     assert np.array_equal(o["out"][:, 0], np.broadcast_to(g["temp_cond_latents"][1, 0], o["out"][:, 0].shape), equal_nan=True)
+
+
+TOP = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "latent_top_*.npz")))
+
+
+def test_latent_top_fixture_set_present():
+    assert len(TOP) == 3
+
+
+@pytest.mark.parametrize("name", TOP)
+def test_top_masks_oracle_vs_golden(golden, name):
+    """The selection-only form (step_single :548-589) with the caller's weight_clamp."""
+    g = golden(name)
+    o = lo.top_masks(g["pred"], g["temp_cond_latents"], g["mask"], g["lambda_ts"], int(g["step_index"]), float(g["weight_clamp"]))
+    assert o["top_masks"].dtype == np.bool_ and np.array_equal(o["top_masks"], g["out_top_masks"])
+    assert np.array_equal(o["cutoff_index"], g["aux_cutoff_index"])
+    assert np.array_equal(o["cutoff_value"], g["aux_cutoff_value"], equal_nan=True)
