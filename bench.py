@@ -418,7 +418,7 @@ def run_ours(args):
         def latent_step():      # the C-ABI call itself, REP diffusion steps back to back (a 50 us kernel: one Python-level
             for _ in range(REP):  # call between two events would time the host, not the device)
                 nat.check(nat.lib().syn3r_latent_guided_replace(nat.ptr(p_l), nat.ptr(cond_l), nat.ptr(m_l), nat.ptr(row_l), 1, Fl, 4,
-                                                                hl, wl, 1, 1, 1, Fl - 2, None, None,
+                                                                hl, wl, 1, Fl - 1, 1, 1, Fl - 2, None, None,
                                                                 torch.cuda.current_stream().cuda_stream), "latent")
         latent_mod.guided_replace_(p_l, c_l, m_l, lam_l, 7)
         latent_step()

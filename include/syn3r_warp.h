@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SYN3R_ABI_VERSION 12
+#define SYN3R_ABI_VERSION 13
 
 enum {
     SYN3R_OK = 0,
@@ -220,12 +220,13 @@ int syn3r_flow_fb_consistency_batched(const float *fwd_flow, const float *bwd_fl
  *     (the reference's torch.sort + index; a radix select here), w = x / (1 + x) with x = 1 / (1 - m_ + 1e-6),
  *     zeroed below 0.51 and where d > cutoff; pred[:,tau] = (1 - w) pred[:,tau] + w cond[tau];
  *   pred[:,0] = cond[0], pred[:,F-1] = cond[F-1] (:1496-1499).
- * cond_latents [F,c,h,w] = temp_cond_latents[1]; mask [mask_batch, F-1, mask_channels, h, w] f32, 1 = hole, as the
- * pipeline passes it (the scheduler prepends the frame of ones itself); lambda_row [F] = lambda_ts[step_index].  All
+ * cond_latents [F,c,h,w] = temp_cond_latents[1]; mask [mask_batch, mask_frames, mask_channels, h, w] f32, 1 = hole, as
+ * the pipeline passes it (the scheduler prepends the frame of ones itself, so frame tau reads mask row tau - 1;
+ * mask_frames is F - 2 = 23 in the SVD pipelines' step_interp* calls, F - 1 = 24 for step_single); lambda_row [F] = lambda_ts[step_index].  All
  * device pointers.  out_cutoff_index / out_cutoff_value [n_tau] optional (cutoff_index_e, cutoff_value). */
 int syn3r_latent_guided_replace(float *pred, const float *cond_latents, const float *mask, const float *lambda_row, int b,
-                                int F, int c, int h, int w, int mask_batch, int mask_channels, int tau0, int n_tau,
-                                int *out_cutoff_index, float *out_cutoff_value, void *stream);
+                                int F, int c, int h, int w, int mask_batch, int mask_frames, int mask_channels, int tau0,
+                                int n_tau, int *out_cutoff_index, float *out_cutoff_value, void *stream);
 
 /* The selection half of the same block as step_single (:548-586) and step_interp (:735-774) use it: identical mask
  * binarisation, sort and cutoff, with the caller's weight_clamp as the lower clamp of lambda (:577, :766) and the
@@ -233,7 +234,7 @@ int syn3r_latent_guided_replace(float *pred, const float *cond_latents, const fl
  * (their index_list runs to 24).  out_top_masks [n_tau, b, c, h, w] u8 0 / 1 (the reference concatenates the frames
  * and prepends a frame of ones, :586-589). */
 int syn3r_latent_top_masks(const float *pred, const float *cond_latents, const float *mask, const float *lambda_row, int b,
-                           int F, int c, int h, int w, int mask_batch, int mask_channels, int tau0, int n_tau,
+                           int F, int c, int h, int w, int mask_batch, int mask_frames, int mask_channels, int tau0, int n_tau,
                            float weight_clamp, uint8_t *out_top_masks, int *out_cutoff_index, float *out_cutoff_value,
                            void *stream);
 

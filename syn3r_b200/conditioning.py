@@ -122,7 +122,10 @@ def fuse_uncertainty_batched(cond_ori: torch.Tensor, gs: torch.Tensor, soft_ori:
 
 def nearby_pairs(n_frames: int, window_radius: int = 1):
     """(pair_src, pair_tgt, pair_first): the (ref_i -> cur_i) warps of diffusionGS.py:1322-1326 in the reference's loop
-    order, grouped by target; pair_first[n] .. pair_first[n+1] are frame n's pairs."""
+    order, grouped by target; pair_first[n] .. pair_first[n+1] are frame n's pairs.  The fusion kernel adds a frame's
+    neighbours in list order, which is torch's mean over a stack of up to 4 tensors (its reduce keeps 4 running
+    accumulators): window_radius <= 2.  The reference uses 1 (diffusionGS.py:1313)."""
+    assert 1 <= window_radius <= 2, "k_nearby_uncertainty follows torch's reduction order for at most 4 neighbours"
     ps, pt, first = [], [], [0]
     for cur in range(n_frames):
         for ref in range(cur - window_radius, cur + window_radius + 1):

@@ -77,16 +77,18 @@ int syn3r_flow_fb_consistency_batched(const float *fwd_flow, const float *bwd_fl
 }
 
 static int launch_latent(float *pred, const float *cond_latents, const float *mask, const float *lambda_row, int b, int F,
-                         int c, int h, int w, int mask_batch, int mask_channels, int tau0, int n_tau, float clamp_lo,
-                         int blend, unsigned char *out_top, int *out_cutoff_index, float *out_cutoff_value, void *stream) {
+                         int c, int h, int w, int mask_batch, int mask_frames, int mask_channels, int tau0, int n_tau,
+                         float clamp_lo, int blend, unsigned char *out_top, int *out_cutoff_index, float *out_cutoff_value, void *stream) {
     SYN3R_REQUIRE(pred && cond_latents && mask && lambda_row, "null required pointer");
     SYN3R_REQUIRE(b > 0 && F >= 2 && c > 0 && h > 0 && w > 0 && mask_channels > 0, "bad sizes");
     SYN3R_REQUIRE(mask_batch == 1 || mask_batch == b, "the mask's batch must be 1 or the latents' batch (broadcast of :1464)");
     SYN3R_REQUIRE(n_tau >= 0 && tau0 >= 1 && tau0 + n_tau <= F, "frame range outside 1 .. F - 1");
+    SYN3R_REQUIRE(mask_frames >= tau0 + n_tau - 1, "mask has fewer frames than the range reads (frame tau reads mask row tau - 1)");
     SYN3R_REQUIRE((size_t)b * c * h * w < (1ull << 24), "b*c*h*w must stay below 2^24 (float32 count of :1479)");
     LatentArgs a;
     a.pred = pred; a.cond = cond_latents; a.mask = mask; a.lambda_row = lambda_row;
     a.b = b; a.F = F; a.c = c; a.hw = h * w; a.bm = mask_batch; a.cm = mask_channels; a.tau0 = tau0; a.n_tau = n_tau;
+    a.Fm = mask_frames;
     a.clamp_lo = clamp_lo; a.blend = blend; a.out_top = out_top;
     a.out_k = out_cutoff_index; a.out_cutoff = out_cutoff_value;
     const size_t key_bytes = (size_t)b * c * h * w * 4, key_cap = 190 * 1024;   // + 34 KB of histograms <= 227 KB
@@ -105,19 +107,19 @@ static int launch_latent(float *pred, const float *cond_latents, const float *ma
 }
 
 int syn3r_latent_guided_replace(float *pred, const float *cond_latents, const float *mask, const float *lambda_row, int b,
-                                int F, int c, int h, int w, int mask_batch, int mask_channels, int tau0, int n_tau,
-                                int *out_cutoff_index, float *out_cutoff_value, void *stream) {
-    return launch_latent(pred, cond_latents, mask, lambda_row, b, F, c, h, w, mask_batch, mask_channels, tau0, n_tau, 0.4f, 1,
+                                int F, int c, int h, int w, int mask_batch, int mask_frames, int mask_channels, int tau0,
+                                int n_tau, int *out_cutoff_index, float *out_cutoff_value, void *stream) {
+    return launch_latent(pred, cond_latents, mask, lambda_row, b, F, c, h, w, mask_batch, mask_frames, mask_channels, tau0, n_tau, 0.4f, 1,
                          nullptr, out_cutoff_index, out_cutoff_value, stream);
 }
 
 int syn3r_latent_top_masks(const float *pred, const float *cond_latents, const float *mask, const float *lambda_row, int b,
-                           int F, int c, int h, int w, int mask_batch, int mask_channels, int tau0, int n_tau,
+                           int F, int c, int h, int w, int mask_batch, int mask_frames, int mask_channels, int tau0, int n_tau,
                            float weight_clamp, uint8_t *out_top_masks, int *out_cutoff_index, float *out_cutoff_value,
                            void *stream) {
     SYN3R_REQUIRE(out_top_masks, "null required pointer");
-    return launch_latent(const_cast<float *>(pred), cond_latents, mask, lambda_row, b, F, c, h, w, mask_batch, mask_channels,
-                         tau0, n_tau, weight_clamp, 0, out_top_masks, out_cutoff_index, out_cutoff_value, stream);
+    return launch_latent(const_cast<float *>(pred), cond_latents, mask, lambda_row, b, F, c, h, w, mask_batch, mask_frames,
+                         mask_channels, tau0, n_tau, weight_clamp, 0, out_top_masks, out_cutoff_index, out_cutoff_value, stream);
 }
 
 size_t syn3r_mean_uncertainty_workspace_bytes(int P) { return P > 0 ? (size_t)P * SYN3R_SC_BLOCKS * sizeof(double) : 0; }

@@ -568,7 +568,7 @@ k_fwd_tile_fx(const TileArgs a) {
                 *pp = make_uint4(clr, clr, clr, clr);
             }
             if (ly >= th || redo) continue;
-            const unsigned q = (unsigned)slot * hw + (unsigned)(ty0 + ly) * W + tx0 + lane * 4;
+            const size_t q = (size_t)slot * hw + (size_t)((ty0 + ly) * W + tx0 + lane * 4);   // 64-bit: n_slots * H * W may pass 2^32
             const unsigned wm[4] = {pl[0].x, pl[0].y, pl[0].z, pl[0].w}, S[4] = {pl[1].x, pl[1].y, pl[1].z, pl[1].w};
             const unsigned i0[4] = {pl[2].x, pl[2].y, pl[2].z, pl[2].w}, i1[4] = {pl[3].x, pl[3].y, pl[3].z, pl[3].w};
             const unsigned i2[4] = {pl[4].x, pl[4].y, pl[4].z, pl[4].w}, n[4] = {pl[5].x, pl[5].y, pl[5].z, pl[5].w};
@@ -585,7 +585,7 @@ k_fwd_tile_fx(const TileArgs a) {
                 st_once_u32(reinterpret_cast<unsigned *>(a.out_mask + q), (unsigned)o[0].m | ((unsigned)o[1].m << 8) |
                                                                           ((unsigned)o[2].m << 16) | ((unsigned)o[3].m << 24), once);
                 if (a.out_f32) {
-                    float4 *f = reinterpret_cast<float4 *>(a.out_f32 + (size_t)q * 3);
+                    float4 *f = reinterpret_cast<float4 *>(a.out_f32 + q * 3);
                     st_once_f4(f, make_float4(o[0].v0, o[0].v1, o[0].v2, o[1].v0), once);
                     st_once_f4(f + 1, make_float4(o[1].v1, o[1].v2, o[2].v0, o[2].v1), once);
                     st_once_f4(f + 2, make_float4(o[2].v2, o[3].v0, o[3].v1, o[3].v2), once);
@@ -594,7 +594,7 @@ k_fwd_tile_fx(const TileArgs a) {
                     unsigned b[12];
 #pragma unroll
                     for (int j = 0; j < 4; ++j) { b[3 * j] = u8_round(o[j].v0); b[3 * j + 1] = u8_round(o[j].v1); b[3 * j + 2] = u8_round(o[j].v2); }
-                    unsigned *u = reinterpret_cast<unsigned *>(a.out_u8 + (size_t)q * 3);
+                    unsigned *u = reinterpret_cast<unsigned *>(a.out_u8 + q * 3);
 #pragma unroll
                     for (int k = 0; k < 3; ++k)
                         st_once_u32(u + k, b[4 * k] | (b[4 * k + 1] << 8) | (b[4 * k + 2] << 16) | (b[4 * k + 3] << 24), once);
@@ -605,7 +605,7 @@ k_fwd_tile_fx(const TileArgs a) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     if (lane * 4 + j >= tw) continue;
-                    const size_t qq = (size_t)q + j;
+                    const size_t qq = q + j;
                     a.out_mask[qq] = (uint8_t)o[j].m;
                     if (a.out_f32) { a.out_f32[3 * qq] = o[j].v0; a.out_f32[3 * qq + 1] = o[j].v1; a.out_f32[3 * qq + 2] = o[j].v2; }
                     if (a.out_u8) {

@@ -22,9 +22,10 @@ namespace syn3r {
 struct LatentArgs {
     float *pred;                 // [b, F, c, hw] predicted clean latents, updated in place
     const float *cond;           // [F, c, hw] = temp_cond_latents[1]
-    const float *mask;           // [bm, F - 1, cm, hw], 1 = hole (frame tau of the reference's mask is row tau - 1 here)
+    const float *mask;           // [bm, Fm, cm, hw], 1 = hole (frame tau of the reference's mask is row tau - 1 here)
     const float *lambda_row;     // [F] = lambda_ts[step_index]
     int b, F, c, hw, bm, cm, tau0, n_tau;
+    int Fm;                      // frames in `mask`: F - 2 as the pipelines pass it to step_interp*, F - 1 for step_single
     float clamp_lo;              // lower clamp of lambda: 0.4 (:1476) or the caller's weight_clamp (:577, :766)
     int blend;                   // 1: the soft blend of :1487-1499 in place; 0: selection only (pred is not written)
     unsigned char *out_top;      // [n_tau, b, c, hw] top_mask = (d <= cutoff) & m (:583, :772, :1483), optional
@@ -59,7 +60,7 @@ k_latent_guided_replace(const LatentArgs a) {
     const float inv_cm = __fdiv_rn(1.0f, (float)a.cm);
     // mean over the mask's channels of ((1 - mask) > 0.5) for pixel pix of mask batch item mb (:1447, :1457)
     auto mean_valid = [&](int mb, int pix) -> float {
-        const float *mp = a.mask + (((size_t)mb * (a.F - 1) + (tau - 1)) * a.cm) * a.hw + pix;
+        const float *mp = a.mask + (((size_t)mb * a.Fm + (tau - 1)) * a.cm) * a.hw + pix;
         float s = 0.0f;
         for (int ch = 0; ch < a.cm; ++ch) s += (__fsub_rn(1.0f, __ldg(mp + (size_t)ch * a.hw)) > 0.5f) ? 1.0f : 0.0f;
         return __fmul_rn(s, inv_cm);

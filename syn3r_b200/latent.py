@@ -28,16 +28,17 @@ def guided_replace_(pred_original_sample: torch.Tensor, temp_cond_latents: torch
     assert temp_cond_latents.shape[1:] == (F, c, h, w) and temp_cond_latents.shape[0] >= 2
     cond = temp_cond_latents[1].to(torch.float32).contiguous()
     m = mask.to(torch.float32).contiguous()
-    assert m.dim() == 5 and m.shape[1] == F - 1 and m.shape[3:] == (h, w)
+    assert m.dim() == 5 and m.shape[3:] == (h, w)
     idx = list(range(1, F - 1)) if index_list is None else [int(i) for i in index_list]
     assert idx == list(range(idx[0], idx[0] + len(idx))) if idx else True, "index_list must be a contiguous range"
+    assert not idx or m.shape[1] >= idx[-1], "frame tau reads mask[:, tau - 1] (the scheduler prepends a frame of ones, :1449)"
     row = lambda_ts[step_index].to(device=p.device, dtype=torch.float32).contiguous()
     assert row.shape == (F,)
     n_tau = len(idx)
     ks = torch.empty(max(n_tau, 1), dtype=torch.int32, device=p.device) if return_cutoffs else None
     cv = torch.empty(max(n_tau, 1), dtype=torch.float32, device=p.device) if return_cutoffs else None
     nat.check(nat.lib().syn3r_latent_guided_replace(nat.ptr(p), nat.ptr(cond), nat.ptr(m), nat.ptr(row), b, F, c, h, w,
-                                                    m.shape[0], m.shape[2], idx[0] if idx else 1, n_tau,
+                                                    m.shape[0], m.shape[1], m.shape[2], idx[0] if idx else 1, n_tau,
                                                     nat.ptr(ks) if return_cutoffs else None,
                                                     nat.ptr(cv) if return_cutoffs else None,
                                                     torch.cuda.current_stream(p.device).cuda_stream),
@@ -47,27 +48,33 @@ def guided_replace_(pred_original_sample: torch.Tensor, temp_cond_latents: torch
 
 def top_masks(pred_original_sample: torch.Tensor, temp_cond_latents: torch.Tensor, mask: torch.Tensor,
               lambda_ts: torch.Tensor, step_index: int, weight_clamp: float, index_list: Optional[Sequence[int]] = None, *,
-              return_cutoffs: bool = False):
+              trailing_ones: bool = False, return_cutoffs: bool = False):
     """The selection-only form of `step_single` (:548-589) / `step_interp` (:735-778): same cutoff as guided_replace_
     with `weight_clamp` as the lower clamp, nothing written to pred.  Returns the reference's top_masks, bool
-    [1, 1 + len(index_list) * b, c, h, w] (frame of ones first).  index_list defaults to 1 .. F-1 (step_single)."""
+    [1, 1 + len(index_list) * b, c, h, w] (frame of ones first).  index_list defaults to 1 .. F-1 (step_single).
+    `trailing_ones=True` is `step_interp`: index_list defaults to 1 .. F-2 and a second frame of ones closes the
+    stack (:775-777), so the result covers all F frames.
+    dtype contract: pred / cond latents float32; the mask is thresholded as float32 `(1 - mask) > 0.5` (:743),
+    which equals the float64 comparison of the non-Prob pipeline for every 0/1-valued or pooled 1/64-step mask."""
     p = pred_original_sample
     assert p.is_cuda and p.dtype == torch.float32 and p.is_contiguous() and p.dim() == 5
     b, F, c, h, w = p.shape
     assert temp_cond_latents.shape[1:] == (F, c, h, w) and temp_cond_latents.shape[0] >= 2
     cond = temp_cond_latents[1].to(torch.float32).contiguous()
     m = mask.to(torch.float32).contiguous()
-    assert m.dim() == 5 and m.shape[1] == F - 1 and m.shape[3:] == (h, w)
-    idx = list(range(1, F)) if index_list is None else [int(i) for i in index_list]
+    assert m.dim() == 5 and m.shape[3:] == (h, w)
+    idx = list(range(1, F - 1 if trailing_ones else F)) if index_list is None else [int(i) for i in index_list]
     assert idx and idx == list(range(idx[0], idx[0] + len(idx))), "index_list must be a contiguous range"
+    assert m.shape[1] >= idx[-1], "frame tau reads mask[:, tau - 1] (the scheduler prepends a frame of ones, :556)"
     row = lambda_ts[step_index].to(device=p.device, dtype=torch.float32).contiguous()
     n_tau = len(idx)
     top = torch.empty((n_tau * b, c, h, w), dtype=torch.uint8, device=p.device)
     ks = torch.empty(n_tau, dtype=torch.int32, device=p.device)
     cv = torch.empty(n_tau, dtype=torch.float32, device=p.device)
     nat.check(nat.lib().syn3r_latent_top_masks(nat.ptr(p), nat.ptr(cond), nat.ptr(m), nat.ptr(row), b, F, c, h, w, m.shape[0],
-                                               m.shape[2], idx[0], n_tau, float(weight_clamp), nat.ptr(top), nat.ptr(ks),
+                                               m.shape[1], m.shape[2], idx[0], n_tau, float(weight_clamp), nat.ptr(top), nat.ptr(ks),
                                                nat.ptr(cv), torch.cuda.current_stream(p.device).cuda_stream),
               "syn3r_latent_top_masks")
-    out = torch.cat([torch.ones((1, 1, c, h, w), dtype=torch.bool, device=p.device), top.bool()[None]], 1)   # :586-589
+    ones = torch.ones((1, 1, c, h, w), dtype=torch.bool, device=p.device)
+    out = torch.cat([ones, top.bool()[None]] + ([ones] if trailing_ones else []), 1)                         # :586-589, :775-777
     return (out, ks, cv) if return_cutoffs else out

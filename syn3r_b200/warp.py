@@ -24,9 +24,11 @@ _ws_cache: dict = {}
 
 
 def _workspace(nbytes: int, device, tag: str) -> torch.Tensor:
-    """Caller-owned workspace, cached per (device, tag) and grown on demand (torch's caching
-    allocator returns 512-byte aligned blocks)."""
-    key = (str(device), tag)
+    """Caller-owned workspace, cached per (device, stream, tag) and grown on demand (torch's caching
+    allocator returns 512-byte aligned blocks).  The workspace holds kernel state (work counters, max-z' keys,
+    block boxes, the redo list), so calls on different streams must not share one; calls on ONE stream are
+    ordered by the stream."""
+    key = (str(device), torch.cuda.current_stream(device).cuda_stream, tag)
     t = _ws_cache.get(key)
     if t is None or t.numel() < nbytes:
         t = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
@@ -34,8 +36,8 @@ def _workspace(nbytes: int, device, tag: str) -> torch.Tensor:
     return t
 
 
-def _stream_ptr() -> int:
-    return torch.cuda.current_stream().cuda_stream
+def _stream_ptr(device=None) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
 
 
 # --------------------------------------------------------------------------------------------
@@ -122,10 +124,11 @@ def forward_warp_batched(rgbd, Kinv_src, pair_par, pair_src, *, pair_slot=None, 
     status = get("status", True, (n,), torch.int32)
     nbytes = L.syn3r_fwd_workspace_bytes(H, W, S, P, n, flags)
     ws = _workspace(nbytes, dev, "fwd")
-    rc = L.syn3r_forward_warp_batched(
-        nat.ptr(rgbd), nat.ptr(depth64), nat.ptr(src_mask), nat.ptr(Kinv_src), nat.ptr(pair_par), nat.ptr(pair_src),
-        nat.ptr(pair_slot), S, P, n, H, W, flags, nat.ptr(rgb_f32), nat.ptr(rgb_u8), nat.ptr(mask), nat.ptr(winner),
-        nat.ptr(flow), nat.ptr(status), ws.data_ptr(), ws.numel(), _stream_ptr())
+    with torch.cuda.device(dev):        # the C side sizes its grid from, and launches on, the CURRENT device
+        rc = L.syn3r_forward_warp_batched(
+            nat.ptr(rgbd), nat.ptr(depth64), nat.ptr(src_mask), nat.ptr(Kinv_src), nat.ptr(pair_par), nat.ptr(pair_src),
+            nat.ptr(pair_slot), S, P, n, H, W, flags, nat.ptr(rgb_f32), nat.ptr(rgb_u8), nat.ptr(mask), nat.ptr(winner),
+            nat.ptr(flow), nat.ptr(status), ws.data_ptr(), ws.numel(), _stream_ptr(dev))
     nat.check(rc, "syn3r_forward_warp_batched")
     return o
 
@@ -197,10 +200,11 @@ def inverse_warp_batched(src_img, src_depth, tgt_depth, K, pair_P, pair_src, pai
         setattr(outs, key, t.data_ptr())
     nbytes = L.syn3r_inv_workspace_bytes(P)
     ws = _workspace(nbytes, dev, "inv")
-    rc = L.syn3r_inverse_warp_batched(
-        nat.ptr(src_img), depth_ptr, depth_stride, nat.ptr(src_bg), nat.ptr(tgt_depth), k_ptr, ki_ptr, nat.ptr(pair_P),
-        nat.ptr(pair_src), nat.ptr(pair_tgt), P, H, W, float(bandwidth), float(thr_depth), float(thr_depth_strict),
-        ctypes.byref(outs), ws.data_ptr(), ws.numel(), _stream_ptr())
+    with torch.cuda.device(dev):
+        rc = L.syn3r_inverse_warp_batched(
+            nat.ptr(src_img), depth_ptr, depth_stride, nat.ptr(src_bg), nat.ptr(tgt_depth), k_ptr, ki_ptr, nat.ptr(pair_P),
+            nat.ptr(pair_src), nat.ptr(pair_tgt), P, H, W, float(bandwidth), float(thr_depth), float(thr_depth_strict),
+            ctypes.byref(outs), ws.data_ptr(), ws.numel(), _stream_ptr(dev))
     nat.check(rc, "syn3r_inverse_warp_batched")
     return o
 
@@ -217,7 +221,8 @@ def consistency_batched(depth1, depth2, K1, K2, pair_T, pair_1, pair_2, out=None
     a1i, p1i = nat.host_f32(torch.inverse(K1t).numpy())
     a2, p2 = nat.host_f32(K2t.numpy())
     err = out if out is not None else torch.empty((P, H, W), dtype=torch.float32, device=depth1.device)
-    rc = L.syn3r_consistency_batched(nat.ptr(depth1), nat.ptr(depth2), p1, p1i, p2, nat.ptr(pair_T), nat.ptr(pair_1),
-                                     nat.ptr(pair_2), P, H, W, nat.ptr(err), _stream_ptr())
+    with torch.cuda.device(depth1.device):
+        rc = L.syn3r_consistency_batched(nat.ptr(depth1), nat.ptr(depth2), p1, p1i, p2, nat.ptr(pair_T), nat.ptr(pair_1),
+                                         nat.ptr(pair_2), P, H, W, nat.ptr(err), _stream_ptr(depth1.device))
     nat.check(rc, "syn3r_consistency_batched")
     return err
