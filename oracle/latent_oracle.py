@@ -17,8 +17,9 @@ and `step_interp` (:735-778), which clamp lambda at the caller's `weight_clamp` 
   pred[:, 0] = temp_cond_latents[1, 0]; pred[:, -1] = temp_cond_latents[1, -1]                (:1496-1499)
 
 A selection (np.partition semantics via a full sort) and exact float32 elementwise work: the bar is bit-exact.
-Parity pinned by tests/golden/latent_*.npz (the reference's statements re-executed with torch,
-tests/golden/make_golden_latent.py).
+Parity pinned by tests/golden/latent_*.npz, latent_top_*.npz, latent_interp_*.npz: outputs of the LIVE patched
+`EulerDiscreteScheduler` of the reference (`step_interp_prob_uncertain`, `step_single`, `step_interp` called on seeded
+inputs; tests/golden/make_golden_latent.py).
 """
 import numpy as np
 
@@ -61,14 +62,15 @@ def guided_replace(pred: np.ndarray, temp_cond_latents: np.ndarray, mask: np.nda
 
 
 def top_masks(pred: np.ndarray, temp_cond_latents: np.ndarray, mask: np.ndarray, lambda_ts: np.ndarray, step_index: int,
-              weight_clamp: float, index_list=None) -> dict:
+              weight_clamp: float, index_list=None, trailing_ones: bool = False) -> dict:
     """scheduling_euler_discrete.py:548-589 (`step_single`; `step_interp` :735-778 is the same with index_list to 23):
     the selection of guided_replace with `torch.clamp(weight, weight_clamp, 1)` (:577), no blend; top_masks is the
     reference's [1, 1 + len(index_list) * b, c, h, w] bool tensor (frames concatenated on dim 0, unsqueezed, a frame
-    of ones prepended, :586-589)."""
+    of ones prepended, :586-589).  trailing_ones: `step_interp` (index_list defaults to 1..F-2, a second frame of
+    ones appended, :775-777).  mask holds at least max(index_list) frames (row tau - 1 is frame tau's)."""
     pred = pred.astype(f32)
     b, F, c, h, w = pred.shape
-    index_list = list(range(1, F)) if index_list is None else list(index_list)
+    index_list = list(range(1, F - 1 if trailing_ones else F)) if index_list is None else list(index_list)
     valid = (f32(1) - mask.astype(f32)) > f32(0.5)
     valid = np.concatenate([np.ones_like(valid[:, :1]), valid], axis=1)
     tops, ks, cuts = [], [], []
@@ -89,5 +91,5 @@ def top_masks(pred: np.ndarray, temp_cond_latents: np.ndarray, mask: np.ndarray,
             ks.append(k)
             cuts.append(cutoff)
     t = np.concatenate(tops, axis=0)[None]
-    t = np.concatenate([np.ones_like(t[:, :1]), t], axis=1)
+    t = np.concatenate([np.ones_like(t[:, :1]), t] + ([np.ones_like(t[:, :1])] if trailing_ones else []), axis=1)
     return dict(top_masks=t, cutoff_index=np.array(ks), cutoff_value=np.array(cuts, f32))

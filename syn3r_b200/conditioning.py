@@ -187,3 +187,158 @@ def consistency_check_from_nearby_images_bw(intrinsics, interpolated_poses, imag
                                want=("warped_img", "soft_mask_reproj"))
     f = nearby_uncertainty_batched(o["soft_mask_reproj"], o["warped_img"], img, up(first, torch.int32))
     return f["uncertainty"], f["intensity_uncertainty"]
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Drop-in `DiffusionGS.warp_images` / `DiffusionGS.warp_images_bw` (SURVEY §8a row a9)
+# ---------------------------------------------------------------------------------------------------------
+
+_plan_cache: dict = {}
+
+
+def _diffusion_size(self):
+    new_width = getattr(self, "diffusion_width", 1024)
+    new_height = getattr(self, "diffusion_height", 576)
+    assert new_width == 1024 and new_height == 576                     # diffusionGS.py:1525, :1382
+    return new_width, new_height
+
+
+def _save_pngs(jobs):
+    """[(path, uint8 array)] -> PNG files, encoded on a small thread pool (zlib releases the GIL)."""
+    import PIL.Image
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(max_workers=8) as ex:
+        list(ex.map(lambda j: PIL.Image.fromarray(j[1]).save(j[0]), jobs))
+
+
+def warp_images(self, intrinsics, interpolated_poses, image_l, image_r=None, depth_l=None, depth_r=None, save_path='',
+                save_file_name_prefix=''):
+    """Drop-in for `DiffusionGS.warp_images` (/root/reference/model/diffusionGS.py:1512-1605): same arguments, same
+    return tuple `(image_o / 255., image_o2 / 255. | None, masks (23|24,72,128) float64 tensor, cond_image list of
+    (576,1024,3) float32)`, same two PNG files per frame under `save_path`.  Bind it as the method
+    (`DiffusionGS.warp_images = syn3r_b200.conditioning.warp_images`) or call it with any object carrying
+    `diffusion_width` / `diffusion_height` (None: 1024 x 576).
+
+    The host side does what the reference does on the host (`cv2.resize` LINEAR / NEAREST of :1531-1549); the 23 or 24
+    `forward_warp` calls of the loop (:1554-1599) with its `i < 12` source switch and the per-frame cv2 / PIL block
+    (:1572-1597) are ONE batched forward warp + ONE post-processing launch (`TrajectoryWarp(post=True)`)."""
+    import os
+    import cv2
+    from . import trajectory, warp as w
+    new_width, new_height = _diffusion_size(self)
+    pose_s_l = interpolated_poses[0]
+    image_l = cv2.resize(image_l, (new_width, new_height), interpolation=cv2.INTER_LINEAR)
+    image_o = image_l
+    depth_l = cv2.resize(depth_l, (new_width, new_height), interpolation=cv2.INTER_NEAREST)
+    pose_s_r = interpolated_poses[-1]
+    interp_num = len(interpolated_poses) - 1
+    assert interp_num == 24                                             # :1544
+    image_o2 = None
+    if image_r is not None:
+        interp_num = interp_num - 1
+        image_r = cv2.resize(image_r, (new_width, new_height), interpolation=cv2.INTER_LINEAR)
+        image_o2 = image_r
+        depth_r = cv2.resize(depth_r, (new_width, new_height), interpolation=cv2.INTER_NEAREST)
+    H, W = new_height, new_width
+    two = image_r is not None
+    S = 2 if two else 1
+    pair_src = np.array([0 if (not two or i < 12) else 1 for i in range(interp_num)], np.int32)        # :1555-1567
+    pair_tgt = np.arange(interp_num, dtype=np.int32)
+    dev = _dev()
+    key = ("fw", S, interp_num, H, W, str(dev))
+    tw = _plan_cache.get(key)
+    if tw is None:
+        tw = _plan_cache[key] = trajectory.TrajectoryWarp(S, interp_num, H, W, pair_src, pair_tgt, device=dev, consistency=False,
+                                                          want_f32=False, want_u8=True, want_winner=False, post=True)
+    pose_src = np.stack([np.asarray(pose_s_l)] + ([np.asarray(pose_s_r)] if two else []))
+    pose_tgt = np.stack([np.asarray(interpolated_poses[i + 1]) for i in range(interp_num)])
+    tw.set_cameras(pose_src, pose_tgt, np.asarray(intrinsics))
+    rgb = np.stack([image_l] + ([image_r] if two else []))
+    dep = np.stack([depth_l] + ([depth_r] if two else []))
+    tw.upload(torch.from_numpy(w.pack_rgbd(rgb, dep)))
+    tw.run()
+    o = tw.out_post
+    png = o["post_mask_png"].cpu().numpy()
+    cond_u8 = o["post_cond_u8"].cpu().numpy()
+    latent = o["post_latent"].cpu().numpy()
+    if int(tw.out_fwd["status"].max().item()) != 0:
+        raise AssertionError("warped colour outside [0, 256] (forward_warp.py:121-125)")
+    jobs = []
+    for i in range(interp_num):
+        stem = os.path.join(save_path, save_file_name_prefix + '_' + str(i).zfill(4))
+        jobs.append((stem + "_mask.png", np.repeat(png[i][:, :, None], 3, axis=2)))                        # :1580
+        jobs.append((stem + ".png", cond_u8[i]))                                                            # :1587
+    _save_pngs(jobs)
+    cond_image = [np.asarray(cond_u8[i], dtype=np.float32) / 255. for i in range(interp_num)]              # :1590
+    masks = torch.from_numpy(latent.astype(np.float64))                                                     # :1592-1600
+    return image_o / 255., (image_o2 / 255. if two else None), masks, cond_image
+
+
+def warp_images_bw(self, intrinsics, interpolated_poses, image_l, image_r=None, depth_l=None, depth_r=None, save_path=None,
+                   save_file_name_prefix='', return_ero_mask=False):
+    """Drop-in for `DiffusionGS.warp_images_bw` (/root/reference/model/diffusionGS.py:1367-1510): same arguments and
+    return values, incl. the `aux` dict when `return_ero_mask` (:1497-1504) and the three PNG files per frame.
+    `self.render_GS(pose=...)` is the caller's 3DGS renderer (outside the hot path) and is called once per frame in
+    the reference's order; the 23 or 24 `inverse_warp` calls (:1438-1441) and the per-frame host block (:1452-1491)
+    are ONE batched backward warp + ONE post-processing launch.  Files are written when `save_path` is not None (the
+    reference raises on `os.path.join(None, ...)`)."""
+    import os
+    import cv2
+    from . import warp as w
+    new_width, new_height = _diffusion_size(self)
+    pose_s_l = interpolated_poses[0]
+    image_l = cv2.resize(image_l, (new_width, new_height), interpolation=cv2.INTER_NEAREST)
+    image_o = image_l
+    depth_l = cv2.resize(depth_l, (new_width, new_height), interpolation=cv2.INTER_NEAREST)
+    interp_num = len(interpolated_poses) - 1
+    assert interp_num == 24                                             # :1395
+    image_o2, pose_s_r = None, None
+    if image_r is not None:
+        interp_num = interp_num - 1
+        pose_s_r = interpolated_poses[-1]
+        image_r = cv2.resize(image_r, (new_width, new_height), interpolation=cv2.INTER_NEAREST)
+        image_o2 = image_r
+        depth_r = cv2.resize(depth_r, (new_width, new_height), interpolation=cv2.INTER_NEAREST)
+    two = depth_r is not None                                           # the source switch keys on depth_r here (:1416)
+    H, W = new_height, new_width
+    tgt = []
+    for i in range(interp_num):                                         # the caller's renderer, in the reference's order
+        _, _rendered_t, rendered_depth_t = self.render_GS(pose=interpolated_poses[i + 1])
+        tgt.append(cv2.resize(rendered_depth_t, (new_width, new_height), interpolation=cv2.INTER_NEAREST))      # :1434
+    dev = _dev()
+    pair_src = np.array([0 if (not two or i < 12) else 1 for i in range(interp_num)], np.int32)
+    pair_tgt = np.arange(interp_num, dtype=np.int32)
+    pose_src = np.stack([np.asarray(pose_s_l, np.float32)] + ([np.asarray(pose_s_r, np.float32)] if two else []))
+    pose_tgt = np.stack([np.asarray(interpolated_poses[i + 1], np.float32) for i in range(interp_num)])
+    up = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a), dtype=dt).to(dev)  # noqa: E731
+    img = up(np.stack([image_l] + ([image_r] if two else [])), torch.float32).permute(0, 3, 1, 2).contiguous()
+    dep = up(np.stack([depth_l] + ([depth_r] if two else [])), torch.float32)
+    tgd = up(np.stack(tgt), torch.float32)
+    iw = w.inverse_warp_batched(img, dep, tgd, np.asarray(intrinsics, np.float32),
+                                up(w.inverse_pair_params(pose_src, pose_tgt, pair_src, pair_tgt), torch.float32),
+                                up(pair_src, torch.int32), up(pair_tgt, torch.int32),
+                                want=("warped_img", "mask_reproj", "soft_mask_reproj"))
+    o = condition_post_batched(iw["mask_reproj"], img_chw=iw["warped_img"], soft=iw["soft_mask_reproj"],
+                               want=("mask_png", "cond_u8", "cond_ori", "latent", "soft_pooled"))
+    png = o["mask_png"].cpu().numpy()
+    cond_u8 = o["cond_u8"].cpu().numpy()
+    latent = o["latent"].cpu().numpy()
+    if save_path is not None:
+        jobs = []
+        for i in range(interp_num):
+            stem = os.path.join(save_path, save_file_name_prefix + '_' + str(i).zfill(4))
+            jobs.append((stem + "_depth.png", np.uint8(tgt[i])))                                            # :1447
+            jobs.append((stem + "_mask.png", np.repeat(png[i][:, :, None], 3, axis=2)))                    # :1460
+            jobs.append((stem + ".png", cond_u8[i]))                                                        # :1471
+        _save_pngs(jobs)
+    cond_image = [np.asarray(cond_u8[i], dtype=np.float32) / 255. for i in range(interp_num)]              # :1475
+    masks = torch.from_numpy(latent.astype(np.float64))                                                     # :1477-1482, :1494
+    ret = (image_o / 255., (image_o2 / 255. if image_r is not None else None), masks, cond_image)
+    if not return_ero_mask:
+        return ret
+    cond_ori = o["cond_ori"].cpu().numpy()
+    aux = {"masks_ero": np.repeat((png // 255)[..., None], 3, axis=3).astype(np.uint8),                    # :1463-1465, :1497
+           "soft_masks_reproj": o["soft_pooled"].cpu().to(dtype=torch.float32),                             # :1486-1496
+           "soft_masks_reproj_ori": (1 - iw["soft_mask_reproj"].cpu().numpy()).astype(np.float32),          # :1485, :1498
+           "cond_images_ori": [cond_ori[i] for i in range(interp_num)]}                                     # :1467
+    return ret + (aux,)

@@ -1,10 +1,10 @@
 """Golden fixtures of the nearby-frame consistency check (second half): tests/golden/nearby_*.npz.
 
 `consistency_check_from_nearby_images_bw` (/root/reference/model/diffusionGS.py:1300-1361) is a method of a class that
-cannot be imported here (FSGS, open3d, diffusers are absent, SURVEY §8c caveat 3).  Its body is a loop around the
-LIVE reference `inverse_warp` (solver_utils/forward_warp.py:185, imported unmodified through make_golden.py's
-'cuda'->'cpu' shim); the generator re-executes the loop's own statements around that call, with device='cpu' and
-without the hard-coded 1024x576 assert so that small frames can be stored.  Run in the build container:
+cannot be imported here (FSGS, open3d, diffusers are absent, SURVEY §8c caveat 3).  The generator slices the METHOD'S
+OWN SOURCE TEXT from the file and exec-s it (tests/golden/ref_exec.py) around the LIVE reference `inverse_warp`
+(solver_utils/forward_warp.py:187, imported unmodified through make_golden.py's 'cuda'->'cpu' shim); no line of it is
+retyped or patched, and each fixture records the slice's SHA-256.  Run in the build container:
 
     python tests/golden/make_golden_nearby.py
 """
@@ -17,44 +17,24 @@ import torch
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, HERE)
 import make_golden as mg  # noqa: E402  (device shim + the live reference modules)
+import ref_exec  # noqa: E402
 
 inverse_warp = mg.ref_fw.inverse_warp
 synth = mg.synth
 
 
-def reference_nearby(intrinsics, interpolated_poses, images, depths, window_radius=1):
-    """diffusionGS.py:1318-1357, statements in the reference's order (device='cuda' -> 'cpu')."""
-    uncertainty_masks = []
-    intensity_uncertainty_masks = []
-    for cur_i in range(len(interpolated_poses)):
-        masks = []
-        warps = []
-        for ref_i in range(cur_i - window_radius, cur_i + window_radius + 1):
-            if ref_i == cur_i or ref_i < 0 or ref_i >= len(interpolated_poses):
-                continue
-            pose_s = interpolated_poses[ref_i]
-            pose_t = interpolated_poses[cur_i]
-            depth_s = depths[ref_i]
-            depth_t = depths[cur_i]
-            image_s = images[ref_i]
-            image_t = images[cur_i]
-            warp_dict = inverse_warp(
-                torch.tensor(image_s, device='cpu', dtype=torch.float32).permute([2, 0, 1]),
-                torch.tensor(depth_s[None], device='cpu'),
-                depth_pseudo=torch.tensor(depth_t[None], device='cpu'),
-                pose1=torch.tensor(pose_s, device='cpu', dtype=torch.float32),
-                pose2=torch.tensor(pose_t, device='cpu', dtype=torch.float32),
-                K=torch.tensor(intrinsics, device='cpu', dtype=torch.float32),
-                bandwidth=10)
-            masks.append(warp_dict['soft_mask_reproj'])
-            warps.append(warp_dict['warped_img'])
-        conf_mask = torch.stack(masks).mean(dim=0)
-        uncertainty_masks.append(1 - conf_mask)
-        warped_image = torch.stack(warps).mean(dim=0)
-        intensity_conf = torch.exp(-((torch.norm(
-            warped_image - torch.tensor(image_t, device='cpu', dtype=torch.float32).permute([2, 0, 1]), dim=0)) / 0.1) ** 3)
-        intensity_uncertainty_masks.append(1 - intensity_conf)
-    return uncertainty_masks, intensity_uncertainty_masks
+def reference_nearby(intrinsics, interpolated_poses, images, depths):
+    """The reference's method itself: `consistency_check_from_nearby_images_bw` (diffusionGS.py:1300-1361) sliced from
+    the file and exec-ed (ref_exec.py) with the live `inverse_warp`, a stub `self` carrying the asserted 1024 x 576
+    diffusion size (the method never uses it: frames of any size run) and a `torch` whose factory calls map the
+    hard-coded device='cuda' to 'cpu'.  No textual patch."""
+    import types
+    fn, tag, desc = ref_exec.exec_function("model/diffusionGS.py", 1300, 1361, "consistency_check_from_nearby_images_bw",
+                                           dict(torch=ref_exec.TorchOnCpu(), np=np, inverse_warp=inverse_warp))
+    assert not desc
+    self = types.SimpleNamespace(diffusion_width=1024, diffusion_height=576)
+    unc, iunc = fn(self, intrinsics, interpolated_poses, images, depths)
+    return unc, iunc, tag
 
 
 def low_contrast_images(rng, N, H, W):
@@ -80,10 +60,11 @@ def main():
                 raised = False
             except RuntimeError:
                 raised = True
-            mg.save(f"nearby_{k}", K=tr.K, poses=tr.pose_src, images=images, depths=tr.depth, raised=np.array(raised))
+            mg.save(f"nearby_{k}", K=tr.K, poses=tr.pose_src, images=images, depths=tr.depth, raised=np.array(raised),
+                    ref_source=np.array(ref_exec.source("model/diffusionGS.py", 1300, 1361)[1]))
             continue
-        unc, iunc = reference_nearby(tr.K, list(tr.pose_src), list(images), list(tr.depth))
-        mg.save(f"nearby_{k}", K=tr.K, poses=tr.pose_src, images=images, depths=tr.depth,
+        unc, iunc, tag = reference_nearby(tr.K, list(tr.pose_src), list(images), list(tr.depth))
+        mg.save(f"nearby_{k}", K=tr.K, poses=tr.pose_src, images=images, depths=tr.depth, ref_source=np.array(tag),
                 out_uncertainty=np.stack([u.numpy() for u in unc]), out_intensity=np.stack([u.numpy() for u in iunc]))
 
 

@@ -63,7 +63,7 @@ def test_guided_replace_sub_range_and_bad_arguments():
     out, _, _ = _run(pred, tcl, mask, lam, 0, index_list=[2, 3, 4])
     assert np.array_equal(out, r["out"], equal_nan=True)
     z = torch.zeros(8, device="cuda")
-    assert nat.lib().syn3r_latent_guided_replace(nat.ptr(z), nat.ptr(z), nat.ptr(z), nat.ptr(z), 1, 8, 1, 1, 1, 1, 1, 0, 3,
+    assert nat.lib().syn3r_latent_guided_replace(nat.ptr(z), nat.ptr(z), nat.ptr(z), nat.ptr(z), 1, 8, 1, 1, 1, 1, 7, 1, 0, 3,
                                                  None, None, None) != 0            # tau0 = 0 is outside 1 .. F - 1
 
 
@@ -84,3 +84,20 @@ def test_top_masks_golden(golden, name):
     assert np.array_equal(ks.cpu().numpy(), g["aux_cutoff_index"])
     assert np.array_equal(cv.cpu().numpy(), g["aux_cutoff_value"], equal_nan=True)
     assert np.array_equal(p.cpu().numpy(), g["pred"], equal_nan=True)                 # pred untouched
+
+
+INTERP = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "latent_interp_*.npz")))
+
+
+@pytest.mark.parametrize("name", INTERP)
+def test_step_interp_top_masks_golden(golden, name):
+    """`step_interp` (:735-778) of the live scheduler: 23 mask frames, clamp 0.4, frames of ones on both ends."""
+    from syn3r_b200 import latent
+    g = golden(name)
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    tm, ks, cv = latent.top_masks(up(g["pred"]), up(g["temp_cond_latents"]), up(g["mask"]), up(g["lambda_ts"]),
+                                  int(g["step_index"]), float(g["weight_clamp"]), trailing_ones=True, return_cutoffs=True)
+    torch.cuda.synchronize()
+    assert tm.shape == g["out_top_masks"].shape and np.array_equal(tm.cpu().numpy(), g["out_top_masks"])
+    assert np.array_equal(ks.cpu().numpy(), g["aux_cutoff_index"])
+    assert np.array_equal(cv.cpu().numpy(), g["aux_cutoff_value"], equal_nan=True)

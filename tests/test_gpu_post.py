@@ -109,11 +109,11 @@ def test_trajectory_run_post_matches_oracle_on_the_plan_outputs():
 FUSION = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "fusion_*.npz")))
 
 
-def _check_fusion(o, ref_unc, ref_masks, ref_cond):
+def _check_fusion(o, ref_unc, ref_masks, ref_cond, rows=slice(None)):
     unc = o["geo_inten_uncertainty"].cpu().numpy()
-    assert np.max(np.abs(unc - ref_unc)) <= 1e-6
+    assert np.max(np.abs(unc[:, rows] - ref_unc)) <= 1e-6
     assert np.max(np.abs(o["masks"].cpu().numpy() - ref_masks)) <= 1e-6
-    band = (np.abs(ref_unc - 0.5) <= 1e-6)[..., None]           # the np.where(unc > 0.5) choice is free inside the band
+    band = (np.abs(unc - 0.5) <= 2e-6)[..., None]               # the np.where(unc > 0.5) choice is free inside the band
     assert ((o["cond_image"].cpu().numpy() == ref_cond) | band).all()
 
 
@@ -121,13 +121,13 @@ def _check_fusion(o, ref_unc, ref_masks, ref_cond):
 def test_fuse_uncertainty_golden(golden, name):
     """SURVEY §8f rank 2 against the reference's statements re-executed with NumPy (float32 exp / pow: 1e-6)."""
     from syn3r_b200 import conditioning as c
-    g = golden(name)
+    from conftest import expand_fusion
+    cond, gs, soft, ref_masks, ref_cond, ref_unc, rows = expand_fusion(golden(name))
     up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
-    o = c.fuse_uncertainty_batched(up(g["in_cond_ori"]), up(g["in_gs"]), up(g["in_soft_ori"]),
-                                   want=("cond_image", "masks", "geo_inten_uncertainty"))
+    o = c.fuse_uncertainty_batched(up(cond), up(gs), up(soft), want=("cond_image", "masks", "geo_inten_uncertainty"))
     torch.cuda.synchronize()
     assert o["masks"].dtype == torch.float32 and o["geo_inten_uncertainty"].dtype == torch.float64
-    _check_fusion(o, g["out_geo_inten_uncertainty"][..., 0], g["out_masks"], g["out_cond_image"])
+    _check_fusion(o, ref_unc, ref_masks, ref_cond, rows)
 
 
 def test_fuse_uncertainty_full_size_vs_oracle():

@@ -1,4 +1,4 @@
-"""CPU: the guided-latent-replacement oracle against the fixtures (scheduler statements re-executed with torch)."""
+"""CPU: the guided-latent-replacement oracle against the fixtures (outputs of the reference's live patched scheduler)."""
 import glob
 import os
 
@@ -42,3 +42,27 @@ def test_top_masks_oracle_vs_golden(golden, name):
     assert o["top_masks"].dtype == np.bool_ and np.array_equal(o["top_masks"], g["out_top_masks"])
     assert np.array_equal(o["cutoff_index"], g["aux_cutoff_index"])
     assert np.array_equal(o["cutoff_value"], g["aux_cutoff_value"], equal_nan=True)
+
+
+INTERP = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "latent_interp_*.npz")))
+
+
+def test_latent_interp_fixture_set_present():
+    assert len(INTERP) == 3
+
+
+@pytest.mark.parametrize("name", INTERP)
+def test_step_interp_top_masks_oracle_vs_golden(golden, name):
+    """`step_interp` (:735-778): frames 1..23, clamp 0.4, a frame of ones on both ends."""
+    g = golden(name)
+    o = lo.top_masks(g["pred"], g["temp_cond_latents"], g["mask"], g["lambda_ts"], int(g["step_index"]), float(g["weight_clamp"]),
+                     trailing_ones=True)
+    assert o["top_masks"].shape == g["out_top_masks"].shape and np.array_equal(o["top_masks"], g["out_top_masks"])
+    assert np.array_equal(o["cutoff_index"], g["aux_cutoff_index"])
+    assert np.array_equal(o["cutoff_value"], g["aux_cutoff_value"], equal_nan=True)
+
+
+@pytest.mark.parametrize("name", LATENT + TOP + INTERP)
+def test_latent_fixtures_come_from_the_live_scheduler(golden, name):
+    v = " ".join(str(x) for x in golden(name)["versions"])
+    assert "live EulerDiscreteScheduler" in v and "sha256=" in v
