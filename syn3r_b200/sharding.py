@@ -135,3 +135,131 @@ class FrameGather:
 
     def _global(self, group_rank: int) -> int:
         return dist.get_global_rank(self.group, group_rank) if self.group is not None else group_rank
+
+
+class PipelinedGather:
+    """The gather of `FrameGather`, issued per CHUNK of a rank's rows on a side stream so that the transfer of one chunk
+    overlaps the kernels of the next ("per-frame ncclSend/Recv on a side stream").
+
+    Every rank cuts its own rows into the same number of chunks; chunk c of every sender is matched by one batch of
+    receives on `dst`.  Usage per step, on every rank:
+
+        g.begin()
+        for c in range(g.n_chunks):
+            a, b = g.bounds(c)            # this rank's rows of chunk c
+            ... enqueue the kernels that produce rows [a, b) on the current stream ...
+            g.push(c, local)              # records an event, sends / receives rows [a, b) behind it on the side stream
+        g.end()                           # the current stream waits for the side stream (gather complete on `dst`)
+    """
+
+    def __init__(self, template: Dict[str, torch.Tensor], counts: Sequence[int], n_chunks: int, dst: int = 0, group=None):
+        self.base = FrameGather(template, counts, dst, group)
+        self.n_chunks = max(1, int(n_chunks))
+        b = self.base
+        self._bounds = [[(b.counts[r] * c) // self.n_chunks for c in range(self.n_chunks + 1)] for r in range(b.world)]
+        dev = next(iter(template.values())).device
+        self.side = torch.cuda.Stream(device=dev) if dev.type == "cuda" else None
+
+    @property
+    def buffers(self):
+        return self.base.buffers
+
+    def bounds(self, c: int) -> Tuple[int, int]:
+        r = self.base.rank
+        return self._bounds[r][c], self._bounds[r][c + 1]
+
+    def bytes_received(self, template) -> int:
+        return self.base.bytes_received(template)
+
+    def begin(self):
+        if self.side is not None:
+            self.side.wait_stream(torch.cuda.current_stream())
+
+    def push(self, c: int, local: Dict[str, torch.Tensor]):
+        b = self.base
+        ev = None
+        if self.side is not None:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream())
+        ctx = torch.cuda.stream(self.side) if self.side is not None else _null()
+        with ctx:
+            if ev is not None:
+                self.side.wait_event(ev)
+            ops = []
+            if b.rank == b.dst:
+                for r in range(b.world):
+                    lo, hi = self._bounds[r][c], self._bounds[r][c + 1]
+                    if hi == lo:
+                        continue
+                    for k in b.keys:
+                        dstv = b.buffers[k][b.offsets[r] + lo:b.offsets[r] + hi]
+                        if r == b.rank:
+                            if dstv.data_ptr() != local[k][lo:hi].data_ptr():      # a plan may already write in place
+                                dstv.copy_(local[k][lo:hi], non_blocking=True)
+                        else:
+                            ops.append(dist.P2POp(dist.irecv, dstv, b._global(r), b.group))
+            else:
+                lo, hi = self._bounds[b.rank][c], self._bounds[b.rank][c + 1]
+                if hi > lo:
+                    for k in b.keys:
+                        ops.append(dist.P2POp(dist.isend, local[k][lo:hi], b._global(b.dst), b.group))
+            if ops:
+                for wk in dist.batch_isend_irecv(ops):
+                    wk.wait()
+
+    def end(self):
+        if self.side is not None:
+            torch.cuda.current_stream().wait_stream(self.side)
+        return self.base.buffers
+
+
+class _null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+def bitpack_masks_wire(wire: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+    """Names of the 0/1 byte masks in a wire (they could travel as bits: 8x smaller); used for reporting only."""
+    return {k: v for k, v in wire.items() if v.dtype == torch.uint8 and k.startswith("mask")}
+
+
+class PeerOutputs:
+    """Outputs of every rank written STRAIGHT into the diffusion rank's memory: one symmetric allocation per key
+    (`torch.distributed._symmetric_memory`, CUDA IPC / fabric handles over NVLink), rank r's plan gets views of rank
+    `dst`'s buffer at its own row offset, so the resolve step of the tile kernel and the consistency kernel store over
+    NVLink while they compute - no staging copy, no send/recv kernel; a barrier at the end makes the rows visible.
+    Raises if symmetric memory is not available on the box (callers fall back to the NCCL gather)."""
+
+    def __init__(self, template: Dict[str, torch.Tensor], counts: Sequence[int], dst: int = 0):
+        import torch.distributed._symmetric_memory as symm
+        self.rank, self.world, self.dst = dist.get_rank(), dist.get_world_size(), dst
+        self.counts = [int(c) for c in counts]
+        self.offsets = [0]
+        for c in self.counts:
+            self.offsets.append(self.offsets[-1] + c)
+        total = self.offsets[-1]
+        self.keys = sorted(template.keys())
+        self.local_views, self.buffers, self._hdl = {}, {}, {}
+        gname = dist.group.WORLD.group_name
+        for k in self.keys:
+            t = template[k]
+            shape = (total,) + tuple(t.shape[1:])
+            mine = symm.empty(shape, dtype=t.dtype, device=t.device)
+            hdl = symm.rendezvous(mine, gname)
+            remote = hdl.get_buffer(dst, shape, t.dtype)
+            self._hdl[k] = hdl
+            lo, hi = self.offsets[self.rank], self.offsets[self.rank + 1]
+            self.local_views[k] = remote[lo:hi]
+            if self.rank == dst:
+                self.buffers[k] = mine
+
+    def bytes_received(self, template) -> int:
+        per_row = sum(int(template[k][0].numel()) * template[k].element_size() for k in self.keys)
+        return per_row * (self.offsets[-1] - self.counts[self.dst])
+
+    def barrier(self):
+        """All ranks' stores are complete and visible on `dst` (stream-ordered barrier of the symmetric-memory handle)."""
+        self._hdl[self.keys[0]].barrier()

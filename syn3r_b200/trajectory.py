@@ -36,22 +36,30 @@ class TrajectoryWarp:
     def __init__(self, S: int, T: int, H: int, W: int, pair_src: Sequence[int], pair_tgt: Sequence[int], *,
                  device=None, consistency: bool = True, want_f32: bool = True, want_u8: bool = False,
                  want_winner: bool = True, bandwidth: float = 20.0, pinned_host: bool = False,
-                 host_outputs: Optional[Sequence[str]] = None, post: bool = False):
+                 host_outputs: Optional[Sequence[str]] = None, post: bool = False, fused: bool = False):
+        """fused=True (extension): the pairs of a target frame share ONE accumulator, outputs are per target frame
+        ([T,H,W,...]); the pairs must be ordered by target (synth.target_major) and there is no per-pair consistency pass."""
         self.S, self.T, self.H, self.W = S, T, H, W
         self.pair_src_h = np.asarray(pair_src, np.int32)
         self.pair_tgt_h = np.asarray(pair_tgt, np.int32)
         self.P = len(self.pair_src_h)
+        self.fused = bool(fused)
+        if self.fused:
+            assert not consistency, "per-pair consistency masks are undefined in FUSED mode (SURVEY §8d config E)"
+            assert np.all(np.diff(self.pair_tgt_h) >= 0), "FUSED mode: order the pairs by target frame"
+        self.N = T if self.fused else self.P          # output slots: target frames (FUSED) or pairs (PAIR)
         self.dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.consistency, self.bandwidth = consistency, float(bandwidth)
         self.want_f32, self.want_u8, self.want_winner = want_f32, want_u8, want_winner
-        d, P = self.dev, self.P
+        d, P = self.dev, self.N
         self.rgbd = torch.empty((S, H, W, 4), dtype=torch.float32, device=d)
         self.tgt_depth = torch.empty((T, H, W), dtype=torch.float32, device=d) if consistency else None
         self.Kinv_src = torch.empty((S, 9), dtype=torch.float64, device=d)
-        self.pair_par = torch.empty((P, 24), dtype=torch.float64, device=d)
-        self.pair_P = torch.empty((P, 2, 16), dtype=torch.float32, device=d) if consistency else None
+        self.pair_par = torch.empty((self.P, 24), dtype=torch.float64, device=d)
+        self.pair_P = torch.empty((self.P, 2, 16), dtype=torch.float32, device=d) if consistency else None
         self.pair_src = torch.from_numpy(self.pair_src_h).to(d)
         self.pair_tgt = torch.from_numpy(self.pair_tgt_h).to(d)
+        self._slot_cache = {}
         self.K_host = None
         self.out_fwd = {}
         self.out_inv = {}
@@ -88,7 +96,7 @@ class TrajectoryWarp:
         """inputs once + outputs once, accumulators zero."""
         hw = self.H * self.W
         out_px = (12 if self.want_f32 else 0) + (3 if self.want_u8 else 0) + 1 + (4 if self.want_winner else 0)
-        b = self.S * hw * 16 + self.P * hw * out_px
+        b = self.S * hw * 16 + self.N * hw * out_px
         if self.consistency:
             b += self.T * hw * 4 + self.P * hw * 5
         return b
@@ -108,7 +116,7 @@ class TrajectoryWarp:
 
     # ---- data ----------------------------------------------------------------------------------
     def _alloc_pinned(self):
-        S, T, H, W, P = self.S, self.T, self.H, self.W, self.P
+        S, T, H, W, P = self.S, self.T, self.H, self.W, self.N
         pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)  # noqa: E731
         self.pinned = {"rgbd": pin((S, H, W, 4), torch.float32)}
         if self.consistency:
@@ -119,7 +127,7 @@ class TrajectoryWarp:
     def _alloc_post(self):
         assert self.want_u8, "the post-processing blanks the uint8 frame: construct with want_u8=True"
         assert self.H % 8 == 0 and self.W % 8 == 0, "post-processing needs H and W to be multiples of 8"
-        P, H, W, d = self.P, self.H, self.W, self.dev
+        P, H, W, d = self.N, self.H, self.W, self.dev
         self.out_post = {"post_mask_png": torch.empty((P, H, W), dtype=torch.uint8, device=d),
                          "post_cond_u8": torch.empty((P, H, W, 3), dtype=torch.uint8, device=d),
                          "post_latent": torch.empty((P, H // 8, W // 8), dtype=torch.uint8, device=d)}
@@ -165,6 +173,17 @@ class TrajectoryWarp:
     # ---- the hot path --------------------------------------------------------------------------
     def _forward(self, sl=slice(None), phases=0):
         out_f = self.out_fwd if sl == slice(None) else {k: v[sl] for k, v in self.out_fwd.items()}
+        if self.fused:                      # sl is a range of SLOTS (target frames); its pairs are contiguous (target-major)
+            t0, t1 = (0, self.T) if sl == slice(None) else (sl.start, sl.stop)
+            key = (t0, t1)
+            if key not in self._slot_cache:
+                p0, p1 = (int(v) for v in np.searchsorted(self.pair_tgt_h, [t0, t1]))
+                self._slot_cache[key] = (p0, p1, (self.pair_tgt[p0:p1] - t0).contiguous())
+            p0, p1, slot = self._slot_cache[key]
+            _w.forward_warp_batched(self.rgbd, self.Kinv_src, self.pair_par[p0:p1], self.pair_src[p0:p1], pair_slot=slot,
+                                    n_slots=t1 - t0, want_f32=self.want_f32, want_u8=self.want_u8,
+                                    want_winner=self.want_winner, is_image=True, out=out_f, phases=phases)
+            return
         _w.forward_warp_batched(self.rgbd, self.Kinv_src, self.pair_par[sl], self.pair_src[sl], want_f32=self.want_f32,
                                 want_u8=self.want_u8, want_winner=self.want_winner, is_image=True, out=out_f,
                                 phases=phases)
@@ -176,8 +195,9 @@ class TrajectoryWarp:
                                 want=("mask_reproj", "soft_mask_reproj"), out=out_i)
 
     def _run_range(self, p0: int, p1: int):
-        """Forward warp (+ consistency masks) of pairs [p0, p1) into the matching slices of the outputs."""
-        sl = slice(None) if (p0 == 0 and p1 == self.P) else slice(p0, p1)
+        """Forward warp (+ consistency masks) of output slots [p0, p1) (pairs; target frames in FUSED mode) into the
+        matching slices of the outputs."""
+        sl = slice(None) if (p0 == 0 and p1 == self.N) else slice(p0, p1)
         if not self.consistency:
             self._forward(sl)
         else:
@@ -188,7 +208,7 @@ class TrajectoryWarp:
 
     def run(self) -> TrajectoryOutputs:
         """Enqueue forward warp (+ consistency masks) for all pairs on the current stream."""
-        self._run_range(0, self.P)
+        self._run_range(0, self.N)
         f, i = self.out_fwd, self.out_inv
         return TrajectoryOutputs(f.get("rgb_f32"), f.get("rgb_u8"), f["mask"], f.get("winner"),
                                  i.get("mask_reproj"), i.get("soft_mask_reproj"), f["status"])
@@ -222,8 +242,8 @@ class TrajectoryWarp:
         # range that reads it, so that with target-major pairs the first range starts after S + a few maps, not all
         self.rgbd.copy_(rgbd_host, non_blocking=True)
         sent = np.zeros(self.T, bool)
-        n = max(1, min(int(chunks), self.P))
-        bounds = [(self.P * c) // n for c in range(n + 1)]
+        n = max(1, min(int(chunks), self.N))
+        bounds = [(self.N * c) // n for c in range(n + 1)]
         for c in range(n):
             p0, p1 = bounds[c], bounds[c + 1]
             if self.consistency:

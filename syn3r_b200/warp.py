@@ -36,6 +36,22 @@ def _workspace(nbytes: int, device, tag: str) -> torch.Tensor:
     return t
 
 
+_last_fwd: dict = {}
+
+
+def redo_items(device) -> int:
+    """Work items ((slot, tile) pairs) the integer tile kernel handed to the fp32 kernel in the LAST forward call on
+    `device` (crowded cells, NaN-poisoned pairs, non-finite colours; normally 0).  Reads the redo counter of the call's
+    workspace (abi.cu fwd_layout: counter block behind the per-pair max-z' keys and NaN flags); synchronises."""
+    ent = _last_fwd.get(str(device))
+    if ent is None:
+        return 0
+    ws, P = ent
+    up = lambda v: (v + 255) // 256 * 256  # noqa: E731
+    off = up(P * 8) + up(P * 4) + 32 * 4
+    return int(ws[off:off + 4].view(torch.int32).item())
+
+
 def _stream_ptr(device=None) -> int:
     return torch.cuda.current_stream(device).cuda_stream
 
@@ -124,6 +140,7 @@ def forward_warp_batched(rgbd, Kinv_src, pair_par, pair_src, *, pair_slot=None, 
     status = get("status", True, (n,), torch.int32)
     nbytes = L.syn3r_fwd_workspace_bytes(H, W, S, P, n, flags)
     ws = _workspace(nbytes, dev, "fwd")
+    _last_fwd[str(dev)] = (ws, P)
     with torch.cuda.device(dev):        # the C side sizes its grid from, and launches on, the CURRENT device
         rc = L.syn3r_forward_warp_batched(
             nat.ptr(rgbd), nat.ptr(depth64), nat.ptr(src_mask), nat.ptr(Kinv_src), nat.ptr(pair_par), nat.ptr(pair_src),

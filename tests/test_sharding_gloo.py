@@ -114,3 +114,69 @@ def test_compact_wire_selects_what_diffusion_consumes():
     assert set(wire) == {"rgb_u8", "mask", "mask_reproj", "soft_mask_reproj"}
     assert sharding.wire_bytes(wire) == P * H * W * (3 + 1 + 1 + 4)
     assert np.isclose(sharding.wire_bytes(wire) / (P * H * W), 9.0)
+
+
+def _worker_pipelined(rank, world, port, T, chunks, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        H, W = 6, 8
+        parts = sharding.partition_units(T, world)
+        t0, t1 = parts[rank]
+        frames = [_fake_frame(t, H, W) for t in range(t0, t1)]
+        proto = _fake_frame(0, H, W)
+        local = {k: (torch.stack([f[k] for f in frames]) if frames else torch.empty((0,) + tuple(proto[k].shape), dtype=proto[k].dtype))
+                 for k in proto}
+        g = sharding.PipelinedGather(local, [e - b for b, e in parts], chunks, dst=0)
+        seen = []
+        for _ in range(2):
+            g.begin()
+            for c in range(g.n_chunks):
+                a, b = g.bounds(c)
+                seen.append((a, b))
+                g.push(c, local)
+            out = g.end()
+        ok = seen[:g.n_chunks] == seen[g.n_chunks:] and seen[0][0] == 0 and seen[g.n_chunks - 1][1] == t1 - t0
+        if rank == 0:
+            for t in range(T):
+                ref = _fake_frame(t, H, W)
+                ok = ok and all(torch.equal(out[k][t], ref[k]) for k in ref)
+        else:
+            ok = ok and out is None
+        dist.barrier()
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,T,chunks", [(2, 7, 3), (3, 4, 4)])
+def test_pipelined_gather_gloo(world, T, chunks):
+    """Per-chunk sends (transfer of one range behind the next range's kernels): every rank cuts its own rows
+    into the same number of chunks, empty chunks included (3 ranks, 4 frames, 4 chunks)."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_pipelined, args=(r, world, port, T, chunks, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res == {r: True for r in range(world)}
+
+
+def test_workload_partition_cuts_trajectories_first_then_frames():
+    """Config D (8 trajectories x 25 frames): 2 / 4 / 8 ranks get whole trajectories; 3 ranks cut inside one.  Config E:
+    100 frames over 8 ranks -> 13,13,13,13,12,12,12,12."""
+    from syn3r_b200 import workload
+    wl = workload.for_config("D_dl3dv")
+    assert wl.frames == 200 and wl.pairs == 400 and wl.mode == "pair"
+    for world in (2, 4, 8):
+        for a, b in sharding.partition_units(wl.frames, world):
+            assert a % 25 == 0 and b % 25 == 0
+    assert wl.frame_owner(0) == (0, 0) and wl.frame_owner(26) == (1, 1) and wl.frame_owner(199) == (7, 24)
+    we = workload.for_config("E_stress")
+    assert we.mode == "fused" and not we.consistency and we.frames == 100
+    assert [b - a for a, b in sharding.partition_units(we.frames, 8)] == [13, 13, 13, 13, 12, 12, 12, 12]
