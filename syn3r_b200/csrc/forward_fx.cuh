@@ -41,6 +41,18 @@ namespace syn3r {
 #define SYN3R_FX_FLAT 2304    /* FLAT kernels: frames of up to this many source blocks (a 1024 x 576 frame), culled in one
                                  pass; listB holds them all */
 #define SYN3R_FX_FLAT_PER_THREAD ((SYN3R_FX_FLAT + SYN3R_TILE_THREADS - 1) / SYN3R_TILE_THREADS)
+// Floor experiments (timing builds only, results are WRONG for every value but 0):
+//   1  sweep 2 skipped            2  sweep 2 with an fp32 projection, no exactness filter, approximate weight (what a
+//   3  no shared-memory atomics      replay of cached sweep-1 geometry would cost)     4  exact weight in sweep 1 too
+#ifndef SYN3R_FX_EXPERIMENT
+#define SYN3R_FX_EXPERIMENT 0
+#endif
+#ifndef SYN3R_FX_BATCH_LDS
+#define SYN3R_FX_BATCH_LDS 1
+#endif
+#ifndef SYN3R_FX_TRASH_SPLIT
+#define SYN3R_FX_TRASH_SPLIT 1
+#endif
 #define SYN3R_FX_MAGIC 12582912.0f          /* 1.5 * 2^23: low mantissa bits of (v + MAGIC) are rint(v) */
 #define SYN3R_FX_MAGIC_BITS 0x4B400000
 
@@ -183,6 +195,29 @@ __device__ __forceinline__ RowProj fx_project(const FxPairRegs &pr, double u0, d
     return o;
 }
 
+#if SYN3R_FX_EXPERIMENT == 3
+#define FX_ATOM(op, addr, val) do { if ((val) == 0x12345u) *(addr) = (val); } while (0)
+#else
+#define FX_ATOM(op, addr, val) op(addr, val)
+#endif
+
+__device__ __forceinline__ RowProj fx_project_f32(const FxPairRegs &pr, float u0, float u1, float u2, float yf, float d,
+                                                  float tx1, float ty1, int tw, int th) {
+    RowProj o;
+    const float q0 = __fmaf_rn(d, __fmaf_rn((float)pr.A[1], yf, u0), (float)pr.b[0]);
+    const float q1 = __fmaf_rn(d, __fmaf_rn((float)pr.A[4], yf, u1), (float)pr.b[1]);
+    const float q2 = __fmaf_rn(d, __fmaf_rn((float)pr.A[7], yf, u2), (float)pr.b[2]);
+    float rc;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(q2));
+    const float lx = __fsub_rn(__fmul_rn(q0, rc), tx1), ly = __fsub_rn(__fmul_rn(q1, rc), ty1);
+    const float rx = rintf(lx), ry = rintf(ly);
+    o.nx1 = (int)rx; o.ny1 = (int)ry;
+    o.fx = __fsub_rn(lx, rx); o.fy = __fsub_rn(ly, ry);
+    o.q2 = (double)q2;
+    o.cand = (unsigned)o.nx1 <= (unsigned)(tw + 1) && (unsigned)o.ny1 <= (unsigned)(th + 1);
+    return o;
+}
+
 // Corner updates of one pixel.  LEAN: all four corners are distinct cells inside the tile (the warp voted so):
 // the corner and the plane fold into immediate offsets of one base address, no validity logic.  Otherwise corners
 // that are not part of the tile go, with weight 0, to the lane's own cell of the trash row behind the tile, so
@@ -208,24 +243,42 @@ __device__ __forceinline__ void fx_corners(const PixelGeom &g, float wsc, const 
     if (SWEEP == 1) {
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-            atomicMax(fx_smem + FX_WMAX * FX_PLANE + oc[c], __float_as_uint(w4[c]));   // positive floats order as ints
-            atomicAdd(fx_smem + FX_N * FX_PLANE + oc[c], 1u);                          // one per sweep-2 update below
-            if (WINNER && (LEAN || w4[c] > 0.0f)) atomicMin(fx_smem + FX_ZKEY * FX_PLANE + oc[c], key);
+            FX_ATOM(atomicMax, fx_smem + FX_WMAX * FX_PLANE + oc[c], __float_as_uint(w4[c]));   // positive floats order as ints
+            FX_ATOM(atomicAdd, fx_smem + FX_N * FX_PLANE + oc[c], 1u);                          // one per sweep-2 update below
+            if (WINNER && (LEAN || w4[c] > 0.0f)) FX_ATOM(atomicMin, fx_smem + FX_ZKEY * FX_PLANE + oc[c], key);
         }
     } else {
         const float c0 = __fmul_rn(px.x, cs_inv), c1 = __fmul_rn(px.y, cs_inv), c2 = __fmul_rn(px.z, cs_inv);
+#if SYN3R_FX_BATCH_LDS
+        // the planes sweep 2 READS (per-cell scale, winner key) are final: all eight look-ups of the pixel go out
+        // together, ahead of the atomics, so that one shared-memory latency is exposed instead of eight
+        unsigned wm4[4], zk4[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            wm4[c] = fx_smem[FX_WMAX * FX_PLANE + oc[c]];
+            if (WINNER) zk4[c] = fx_smem[FX_ZKEY * FX_PLANE + oc[c]];
+        }
+#endif
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             unsigned *q4 = fx_smem + oc[c];
+#if SYN3R_FX_BATCH_LDS
+            const unsigned wm = wm4[c];
+#else
             const unsigned wm = q4[FX_WMAX * FX_PLANE];
+#endif
             const float sc = __uint_as_float(((254u + SYN3R_FX_BITS) << 23) - (wm & 0x7f800000u));
             const float q = __fmul_rn(w4[c], sc);                           // in [0, 2^22)
-            atomicAdd(q4 + FX_S * FX_PLANE, __float_as_uint(__fadd_rn(q, SYN3R_FX_MAGIC)));
-            atomicAdd(q4 + FX_I0 * FX_PLANE, __float_as_uint(__fmaf_rn(q, c0, SYN3R_FX_MAGIC)));
-            atomicAdd(q4 + FX_I1 * FX_PLANE, __float_as_uint(__fmaf_rn(q, c1, SYN3R_FX_MAGIC)));
-            atomicAdd(q4 + FX_I2 * FX_PLANE, __float_as_uint(__fmaf_rn(q, c2, SYN3R_FX_MAGIC)));
+            FX_ATOM(atomicAdd, q4 + FX_S * FX_PLANE, __float_as_uint(__fadd_rn(q, SYN3R_FX_MAGIC)));
+            FX_ATOM(atomicAdd, q4 + FX_I0 * FX_PLANE, __float_as_uint(__fmaf_rn(q, c0, SYN3R_FX_MAGIC)));
+            FX_ATOM(atomicAdd, q4 + FX_I1 * FX_PLANE, __float_as_uint(__fmaf_rn(q, c1, SYN3R_FX_MAGIC)));
+            FX_ATOM(atomicAdd, q4 + FX_I2 * FX_PLANE, __float_as_uint(__fmaf_rn(q, c2, SYN3R_FX_MAGIC)));
             if (WINNER)     // branch-free: a corner that does not hold the cell's key offers the neutral element
-                atomicMin(q4 + FX_IDX * FX_PLANE, ((LEAN || w4[c] > 0.0f) && q4[FX_ZKEY * FX_PLANE] == key) ? i : ~0u);
+#if SYN3R_FX_BATCH_LDS
+                FX_ATOM(atomicMin, q4 + FX_IDX * FX_PLANE, ((LEAN || w4[c] > 0.0f) && zk4[c] == key) ? i : ~0u);
+#else
+                FX_ATOM(atomicMin, q4 + FX_IDX * FX_PLANE, ((LEAN || w4[c] > 0.0f) && q4[FX_ZKEY * FX_PLANE] == key) ? i : ~0u);
+#endif
             asm volatile("" ::: "memory");          // one corner at a time: keeps the live range of the 16 addends short
         }
     }
@@ -248,7 +301,8 @@ __device__ __forceinline__ void fx_rows2(const TileArgs &a, const double2 *__res
         const float lhs = __fmul_rn(fminf(fabsf(rp[j].fx), fabsf(rp[j].fy)), zf);
         const float rhs = __fmaf_rn(zf, pr.k2, __fmaf_rn(df, pr.k1, pr.k0));
         bool slow = !(lhs > rhs);
-        if (WINNER)     // z-key = high word of z': ambiguous when the low word is within 2^14 ulps of a carry, or
+        if (SYN3R_FX_EXPERIMENT == 2 && SWEEP == 2) slow = false;
+        else if (WINNER)     // z-key = high word of z': ambiguous when the low word is within 2^14 ulps of a carry, or
                         // when the fast z' is not known to 2^-39 relative
             slow = slow || ((unsigned)__double2loint(rp[j].q2) + 16384u < 32768u) ||
                    !(__fmul_rn(zf, 1.8e-12f) > __fmaf_rn(df, pr.k3, pr.k4));
@@ -268,7 +322,7 @@ __device__ __forceinline__ void fx_rows2(const TileArgs &a, const double2 *__res
     }
     if (!__any_sync(0xffffffffu, any[0] || any[1])) return;
     float wsc[2];
-    if (SWEEP == 1 && pr.upper_ok) {
+    if ((SWEEP == 1 && pr.upper_ok && SYN3R_FX_EXPERIMENT != 4) || (SYN3R_FX_EXPERIMENT == 2 && SWEEP == 2)) {
 #pragma unroll
         for (int j = 0; j < 2; ++j) wsc[j] = fx_weight_upper(pr.cexp_f, __double2float_rn(g[j].z));
     } else {
@@ -323,12 +377,78 @@ __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__res
             pxa = ld_keep_f4(src, keep);
             pxb = pxa;
         }
+#if SYN3R_FX_EXPERIMENT == 2
+        const RowProj rp[2] = {SWEEP == 2 ? fx_project_f32(pr, (float)u0, (float)u1, (float)u2, (float)y, px[0].w, (float)tx1d, (float)ty1d, tw, th)
+                                          : fx_project(pr, u0, u1, u2, yd, (double)px[0].w, tx1d, ty1d, tw, th),
+                               SWEEP == 2 ? fx_project_f32(pr, (float)u0, (float)u1, (float)u2, (float)(y + 1), px[1].w, (float)tx1d, (float)ty1d, tw, th)
+                                          : fx_project(pr, u0, u1, u2, __dadd_rn(yd, 1.0), (double)px[1].w, tx1d, ty1d, tw, th)};
+#else
         const RowProj rp[2] = {fx_project(pr, u0, u1, u2, yd, (double)px[0].w, tx1d, ty1d, tw, th),
                                fx_project(pr, u0, u1, u2, __dadd_rn(yd, 1.0), (double)px[1].w, tx1d, ty1d, tw, th)};
+#endif
         const bool cand[2] = {rp[0].cand && live, rp[1].cand && live && (r + 1 < rows)};
         const unsigned i[2] = {ia, ia + (unsigned)W};
         fx_rows2<WINNER, SWEEP>(a, logtab, pr, rp, px, cand, p, s, x, y, i, tx0, ty0, tw, th, cs_inv, lane);
         __syncwarp();
+    }
+}
+
+// One sweep over the culled block list (sm.listB, nB blocks) as a software-pipelined STREAM of row pairs: while the
+// warp works on row pair n, the two float4 rows of pair n+1 are in flight from L2 and the claim of pair n+2 (a
+// shared-memory counter) is in flight too, so neither the L2 latency nor the claim is exposed at a work-unit
+// boundary, and the unit of the dynamic scheduler is one iteration (2 x 32 px): short tails at the barrier that ends
+// the sweep.  (The former fx_block took 4-row units and exposed one L2 round trip + one claim per unit.)
+#ifndef SYN3R_FX_STREAM
+#define SYN3R_FX_STREAM 1
+#endif
+template <bool WINNER, int SWEEP>
+__device__ __forceinline__ void fx_stream(const TileArgs &a, const FxAux &sm, const FxPairRegs &pr, int p, int s, int nB,
+                                          int tx0, int ty0, int tw, int th, int lane, float cs_inv) {
+    const int W = a.g.W, H = a.g.H;
+    const int total = nB * (SYN3R_BLK_H / 2);
+    int *ctr = &sm.ctl[SWEEP == 1 ? 4 : 5];
+    const uint64_t keep = l2_policy_evict_last();
+    const float4 *frame = a.rgbd + (size_t)s * (size_t)(H * W);
+    const unsigned ibase = (unsigned)s * (unsigned)(H * W);
+    const double tx1d = (double)(tx0 - 1), ty1d = (double)(ty0 - 1);
+    int kraw = 0;
+    if (lane == 0) kraw = atomicAdd(ctr, 1);
+    int k = __shfl_sync(0xffffffffu, kraw, 0);
+    if (lane == 0) kraw = atomicAdd(ctr, 1);                    // the claim after that: consumed one iteration later
+    if (k >= total) return;
+    int x, y;
+    float4 pxa, pxb;
+    auto fetch = [&](int kk) {
+        const int org = sm.listB[kk >> 2];                      // (by0 << 16) | bx0; SYN3R_BLK_H / 2 = 4 row pairs per block
+        x = (org & 0xffff) + lane;
+        y = (org >> 16) + ((kk & 3) << 1);
+        const float4 *r0 = frame + (size_t)(min(y, H - 1) * W + min(x, W - 1));
+        pxa = ld_keep_f4(r0, keep);
+        pxb = ld_keep_f4(r0 + ((y + 1 < H) ? W : 0), keep);
+    };
+    fetch(k);
+    for (;;) {
+        const int kn = __shfl_sync(0xffffffffu, kraw, 0);
+        if (lane == 0) kraw = atomicAdd(ctr, 1);
+        const float4 px[2] = {pxa, pxb};
+        const int cx = x, cy = y;
+        if (kn < total) fetch(kn);
+        {
+            const bool live = cx < W;
+            // (double) of a non-negative int without a conversion instruction: 2^52 + v has v in its low word
+            const double xd = __dsub_rn(__hiloint2double(0x43300000, cx), 4503599627370496.0);
+            const double yd = __dsub_rn(__hiloint2double(0x43300000, cy), 4503599627370496.0);
+            const double u0 = __fma_rn(pr.A[0], xd, pr.A[2]), u1 = __fma_rn(pr.A[3], xd, pr.A[5]),
+                         u2 = __fma_rn(pr.A[6], xd, pr.A[8]);
+            const RowProj rp[2] = {fx_project(pr, u0, u1, u2, yd, (double)px[0].w, tx1d, ty1d, tw, th),
+                                   fx_project(pr, u0, u1, u2, __dadd_rn(yd, 1.0), (double)px[1].w, tx1d, ty1d, tw, th)};
+            const bool cand[2] = {rp[0].cand && live && cy < H, rp[1].cand && live && cy + 1 < H};
+            const unsigned ia = ibase + (unsigned)(cy * W + (live ? cx : 0));
+            const unsigned i[2] = {ia, ia + (unsigned)W};
+            fx_rows2<WINNER, SWEEP>(a, sm.logtab, pr, rp, px, cand, p, s, cx, cy, i, tx0, ty0, tw, th, cs_inv, lane);
+            __syncwarp();
+        }
+        if (kn >= total) break;
     }
 }
 
@@ -347,6 +467,9 @@ __device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, cons
     const int tw = tx1 - tx0 + 1, th = ty1 - ty0 + 1;
     int *ctl = sm.ctl;
     auto run_list = [&](int nB) {
+#if SYN3R_FX_STREAM && SYN3R_FX_EXPERIMENT == 0
+        fx_stream<WINNER, SWEEP>(a, sm, pr, p, s, nB, tx0, ty0, tw, th, lane, cs_inv);
+#else
         for (;;) {
             int k = 0;
             if (lane == 0) k = atomicAdd(&ctl[SWEEP == 1 ? 4 : 5], 1);
@@ -356,6 +479,7 @@ __device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, cons
             fx_block<WINNER, SWEEP>(a, sm.logtab, pr, p, s, org & 0xffff, (org >> 16) + (k % SYN3R_FX_UNITS) * SYN3R_FX_UNIT_ROWS, tx0, ty0,
                                     tw, th, lane, cs_inv);
         }
+#endif
     };
     if (SWEEP == 2 && reuse_list) {       // the list sweep 1 built is complete: no culling, no barrier
         run_list(ctl[2]);
@@ -528,7 +652,8 @@ k_fwd_tile_fx(const TileArgs a) {
                 fx_pair<WINNER, 1, FLAT>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, true, cs_inv);
                 __syncthreads();
                 scan_crowded();
-                fx_pair<WINNER, 2, FLAT>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, FLAT || ctl[6] != 0, false, cs_inv);
+                if (SYN3R_FX_EXPERIMENT != 1)
+                    fx_pair<WINNER, 2, FLAT>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, FLAT || ctl[6] != 0, false, cs_inv);
             }
             __syncthreads();
         } else {                                               // FUSED mode: every pair of the slot, per sweep
@@ -556,7 +681,17 @@ k_fwd_tile_fx(const TileArgs a) {
         bool bad = false;
         const int tw = tx1 - tx0 + 1, th = ty1 - ty0 + 1;
         const bool vec = (tw == SYN3R_TILE_W) && ((W & 3) == 0);
+#if SYN3R_FX_TRASH_SPLIT
+        // the trash row (row TILE_H, cleared only) is shared out over all threads: with it in the row loop one warp of
+        // 24 would make a third trip for 49 rows
+        for (int k = tid; k < NPL * SYN3R_TILE_W; k += SYN3R_TILE_THREADS) {
+            const int pl = k / SYN3R_TILE_W;
+            fx_smem[pl * CELLS + FX_CELLS + (k - pl * SYN3R_TILE_W)] = (pl >= FX_ZKEY) ? ~0u : (pl == FX_WMAX ? 0x3f800000u : 0u);
+        }
+        for (int ly = warp; ly < SYN3R_TILE_H; ly += nwarps) {
+#else
         for (int ly = warp; ly <= SYN3R_TILE_H; ly += nwarps) {          // row TILE_H = the trash row (cleared only)
+#endif
             const int c4 = ly * SYN3R_TILE_W + lane * 4;       // this lane's 4 consecutive cells of the row
             uint4 pl[8];
 #pragma unroll
