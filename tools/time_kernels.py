@@ -17,7 +17,7 @@ cfg = sys.argv[1] if len(sys.argv) > 1 else "B_svd"
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 10
 S, T, H, W = synth.CONFIGS[cfg]
 tr = synth.make_trajectory(S, T, H, W, seed=0)
-tw = trajectory.from_synth(tr, want_f32=True, want_u8=False, want_winner=True)
+tw = trajectory.from_synth(tr, want_f32=True, want_u8=False, want_winner=os.environ.get("SYN3R_TIME_NO_WINNER") != "1")
 tw.upload(torch.from_numpy(w.pack_rgbd(tr.rgb, tr.depth)), torch.from_numpy(tr.depth_tgt))
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
@@ -47,6 +47,6 @@ if os.environ.get("SYN3R_TIME_CHECK") == "1":
     o = tw.run()
     torch.cuda.synchronize()
     res["check"] = {"mask_sum": int(o.mask.sum().item()), "rgb_sum": float(o.rgb_f32.double().sum().item()),
-                    "winner_sum": int(o.winner.long().sum().item()), "reproj_sum": int(o.mask_reproj.sum().item()),
+                    "winner_sum": int(o.winner.long().sum().item()) if o.winner is not None else None, "reproj_sum": int(o.mask_reproj.sum().item()),
                     "soft_sum": float(o.soft_mask_reproj.double().sum().item()), "redo": w.redo_items(o.mask.device)}
 print(json.dumps(res))
