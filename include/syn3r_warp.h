@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SYN3R_ABI_VERSION 13
+#define SYN3R_ABI_VERSION 14
 
 enum {
     SYN3R_OK = 0,
@@ -73,6 +73,16 @@ const char *syn3r_last_error(void);
  * mode 1: arbitrary bit patterns (denormals, inf, NaN included). */
 int syn3r_selftest_ddiv2(unsigned long long n, unsigned long long seed, int mode, unsigned long long *mismatches,
                          void *stream);
+
+/* Device self-test: the constant-divisor division of the lean consistency kernel (x / c through the correctly
+ * rounded reciprocal and two Markstein corrections; the divisors are (W-1)/2 and (H-1)/2 of consistency.py:71-73)
+ * against div.rn.f32 for the `count` float bit patterns x = first, first+1, ...; adds the number of differing
+ * quotients to mismatch_dev[0] and leaves the bit pattern of one such x in mismatch_dev[1] (device u64[2],
+ * caller-zeroed).  finite_only != 0 skips x = +-inf / NaN and quotients below 2^-30 (where the kernel's next steps
+ * give the same result either way, inverse_kernels.cuh).
+ * *rc_out (host, nullable) receives the reciprocal the library uses, 0 if it keeps the IEEE division for this c. */
+int syn3r_selftest_div_const(float c, unsigned long long first, unsigned long long count, int finite_only,
+                             unsigned long long *mismatch_dev, float *rc_out, void *stream);
 
 /* Number of SMs / max opt-in shared memory of the current device (host query, cached). */
 int syn3r_device_info(int *sm_count, int *smem_optin_bytes, int *cc_major, int *cc_minor);

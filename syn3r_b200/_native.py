@@ -22,7 +22,7 @@ FWD_LEGACY_GLOBAL = 1 << 4
 FWD_FP32_TILE = 1 << 5
 FWD_PHASE_ZMAX, FWD_PHASE_SPLAT, FWD_PHASE_RESOLVE = 1 << 8, 1 << 9, 1 << 10
 
-ABI_VERSION = 13
+ABI_VERSION = 14
 
 c_void_p, c_int, c_size_t, c_float = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t, ctypes.c_float
 
@@ -43,6 +43,8 @@ SIGNATURES = {
     "syn3r_version": (c_int, []),
     "syn3r_last_error": (ctypes.c_char_p, []),
     "syn3r_selftest_ddiv2": (c_int, [ctypes.c_ulonglong, ctypes.c_ulonglong, c_int, c_void_p, c_void_p]),
+    "syn3r_selftest_div_const": (c_int, [c_float, ctypes.c_ulonglong, ctypes.c_ulonglong, c_int, c_void_p,
+                                         ctypes.POINTER(c_float), c_void_p]),
     "syn3r_device_info": (c_int, [ctypes.POINTER(c_int)] * 4),
     "syn3r_fwd_workspace_bytes": (c_size_t, [c_int] * 6),
     "syn3r_forward_warp_batched": (c_int, [c_void_p] * 7 + [c_int] * 6 + [c_void_p] * 7 + [c_size_t, c_void_p]),

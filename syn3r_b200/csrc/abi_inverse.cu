@@ -20,6 +20,25 @@ dim3 stride_grid2(size_t n, int per_block, int ny) {
     return dim3((unsigned)gx, (unsigned)ny, 1);
 }
 
+// RN(1 / c) as a float, or 0 when div_const_rn (inverse_kernels.cuh) must not be used for this divisor: c not a
+// positive normal number of moderate size, or its mantissa all ones (the one case Markstein's theorem excludes).
+// 1 - c r is exact in double (24 x 24 bits), so the candidate with the smallest residual is the nearest float.
+float rounded_reciprocal(float c) {
+    if (!(c >= 1.0f / 1048576.0f && c <= 1048576.0f)) return 0.0f;
+    uint32_t bits;
+    memcpy(&bits, &c, 4);
+    if ((bits & 0x7fffffu) == 0x7fffffu) return 0.0f;
+    float r = (float)(1.0 / (double)c);
+    float best = r;
+    double be = fabs(1.0 - (double)c * (double)r);
+    const float cand[2] = {nextafterf(r, 0.0f), nextafterf(r, INFINITY)};
+    for (int k = 0; k < 2; ++k) {
+        const double e = fabs(1.0 - (double)c * (double)cand[k]);
+        if (e < be) { be = e; best = cand[k]; }
+    }
+    return best;
+}
+
 CamF32 make_cam(const float *K1, const float *K1inv, const float *K2, int H, int W) {
     CamF32 c;
     memcpy(c.K1, K1, sizeof(c.K1));
@@ -29,6 +48,8 @@ CamF32 make_cam(const float *K1, const float *K1inv, const float *K2, int H, int
     c.half_hm1 = (float)((double)(H - 1) / 2.0);
     c.half_w = (float)W / 2.0f;
     c.half_h = (float)H / 2.0f;
+    c.rc_wm1 = rounded_reciprocal(c.half_wm1);
+    c.rc_hm1 = rounded_reciprocal(c.half_hm1);
     return c;
 }
 
@@ -108,6 +129,18 @@ int syn3r_inverse_warp_batched(const float *src_img, const float *src_depth, int
     k_inverse_warp<<<g, 256, 0, st>>>(cam, pr, src_img, src_depth, src_depth_stride, src_bg, tgt_depth, H, W, bandwidth, thr_depth,
                                       thr_depth_strict, *out, ws);
     return check_cuda(cudaGetLastError(), "inverse_warp_batched launches");
+}
+
+int syn3r_selftest_div_const(float c, unsigned long long first, unsigned long long count, int finite_only,
+                              unsigned long long *mismatch_dev, float *rc_out, void *stream) {
+    SYN3R_REQUIRE(mismatch_dev, "null required pointer");
+    int rc = check_device();
+    if (rc != SYN3R_OK) return rc;
+    const float r = rounded_reciprocal(c);
+    if (rc_out) *rc_out = r;
+    if (r == 0.0f) return SYN3R_OK;                         // the kernels use the IEEE division for this divisor
+    k_selftest_div_const<<<sm_count() * 8, 256, 0, (cudaStream_t)stream>>>(first, count, c, r, mismatch_dev, finite_only);
+    return check_cuda(cudaGetLastError(), "k_selftest_div_const");
 }
 
 int syn3r_consistency_batched(const float *depth1, const float *depth2, const float *K1, const float *K1inv,

@@ -44,6 +44,8 @@ namespace syn3r {
 // Floor experiments (timing builds only, results are WRONG for every value but 0):
 //   1  sweep 2 skipped            2  sweep 2 with an fp32 projection, no exactness filter, approximate weight (what a
 //   3  no shared-memory atomics      replay of cached sweep-1 geometry would cost)     4  exact weight in sweep 1 too
+//   5  the floor of the formulation: ONE sweep that loads and projects every culled row and stops there (the vote on
+//      the projected cells keeps the arithmetic alive), then the resolve step with all its output stores
 #ifndef SYN3R_FX_EXPERIMENT
 #define SYN3R_FX_EXPERIMENT 0
 #endif
@@ -293,6 +295,11 @@ __device__ __forceinline__ void fx_rows2(const TileArgs &a, const double2 *__res
                                          int s, int x, int y, const unsigned (&i)[2], int tx0, int ty0, int tw, int th,
                                          float cs_inv, int lane) {
     if (!__any_sync(0xffffffffu, cand[0] || cand[1])) return;               // nothing of these two rows near the tile
+    if (SYN3R_FX_EXPERIMENT == 5) {
+        if (__all_sync(0xffffffffu, rp[0].nx1 == 12345 && rp[1].ny1 == 54321 && rp[0].fx == 7.0f && rp[1].fy == 3.0f))
+            fx_smem[lane] = 1u;
+        return;
+    }
     PixelGeom g[2];
     bool any[2], full[2];
 #pragma unroll
@@ -652,7 +659,7 @@ k_fwd_tile_fx(const TileArgs a) {
                 fx_pair<WINNER, 1, FLAT>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, true, cs_inv);
                 __syncthreads();
                 scan_crowded();
-                if (SYN3R_FX_EXPERIMENT != 1)
+                if (SYN3R_FX_EXPERIMENT != 1 && SYN3R_FX_EXPERIMENT != 5)
                     fx_pair<WINNER, 2, FLAT>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, FLAT || ctl[6] != 0, false, cs_inv);
             }
             __syncthreads();

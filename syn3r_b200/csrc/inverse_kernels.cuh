@@ -28,7 +28,42 @@ struct CamF32 {            // shared by every pair of a call
     float K1[9], K1inv[9], K2[9];
     float half_wm1, half_hm1;   // (float)((W-1)/2.0), (float)((H-1)/2.0)  consistency.py:71-73
     float half_w, half_h;       // W/2, H/2 (grid_sample un-normalise)
+    float rc_wm1, rc_hm1;       // correctly rounded 1 / half_wm1, 1 / half_hm1 (0 = not usable: IEEE division instead)
 };
+
+// x / c for a divisor c that is the same for every pixel, with rc = RN(1 / c) found on the host: two Markstein
+// corrections.  q0 = RN(x rc) is within 2 ulps of x / c; r = x - c q exactly (one FMA), so q1 = RN(q0 + r0 rc) is a
+// faithful quotient and q2 = RN(q1 + r1 rc) the correctly rounded one (Markstein's theorem: rc correctly rounded,
+// mantissa of c not all ones - checked on the host), i.e. the bits of __fdiv_rn(x, c), in 5 instructions instead of
+// the 11 of the IEEE sequence (MUFU.RCP, FCHK, 5 FFMA, 3 branch / reconvergence).  The theorem needs x / c to stay
+// in the normal range and the remainders not to underflow: an x of +-inf gives NaN here (inf - inf) where the division
+// gives inf, and a quotient below ~2^-100 may differ in its last bit; in both cases the caller's next steps (- 1,
+// un-normalise, floor, bounds test) produce the same values either way (inf and NaN both end as NaN weights and no
+// tap; a quotient under 2^-25 disappears in the `- 1`), which is why this is only used where it is (k_reproj_masks:
+// the grid normalisation).
+// tests/test_gpu_parity.py::test_const_division_exhaustive compares all 2^32 x for the divisors of the benchmark sizes.
+__device__ __forceinline__ float div_const_rn(float x, float c, float rc) {
+    const float q0 = __fmul_rn(x, rc);
+    const float q1 = __fmaf_rn(__fmaf_rn(-c, q0, x), rc, q0);
+    return __fmaf_rn(__fmaf_rn(-c, q1, x), rc, q1);
+}
+
+// self-test of div_const_rn against div.rn.f32 over a range of x bit patterns; *mismatch counts differing results
+// (two NaNs count as equal)
+__global__ void k_selftest_div_const(unsigned long long first, unsigned long long count, float c, float rc,
+                                     unsigned long long *__restrict__ mismatch, int finite_only) {
+    unsigned long long bad = 0;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < count;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const float x = __uint_as_float((unsigned)(first + i));
+        const float a = div_const_rn(x, c, rc), b = __fdiv_rn(x, c);
+        const bool same = (__float_as_uint(a) == __float_as_uint(b)) || (a != a && b != b);
+        // |quotient| < 2^-30: the caller's `- 1.0f` gives -1 whatever the last bits of the quotient are
+        const bool skip = finite_only && (!(fabsf(x) < 3.0e38f) || fabsf(b) < 9.3132257e-10f);
+        if (!same && !skip) { ++bad; mismatch[1] = (unsigned)(first + i); }
+    }
+    if (bad) atomicAdd(mismatch, bad);
+}
 
 // A.3: round-trip reprojection error in pixels for frame-1 pixel (x,y) with depth d1.
 // T12 = pose2 @ inv(pose1), T21 = pose1 @ inv(pose2) (consistency.py:39), row-major 4x4.
@@ -256,6 +291,7 @@ k_reproj_masks(CamF32 c, InvPairs pr, const float *__restrict__ src_depth, const
     const float xn = __fdiv_rn(__fsub_rn(xf, cx), fx);                        // :208
     const float kx0 = __fmul_rn(c.K1inv[0], xf), kx1 = __fmul_rn(c.K1inv[3], xf), kx2 = __fmul_rn(c.K1inv[6], xf);
     const float Wf = (float)W, Hf = (float)H;
+    const bool fastc = c.rc_wm1 != 0.0f && c.rc_hm1 != 0.0f;
     const int rows = min(SYN3R_RM_ROWS, H - y0);
     float z_next = __ldg(td + (size_t)y0 * W + x);            // one row ahead: the DRAM latency hides behind a row of math
     for (int r = 0; r < rows; ++r) {
@@ -282,17 +318,29 @@ k_reproj_masks(CamF32 c, InvPairs pr, const float *__restrict__ src_depth, const
         const float p0 = dot3_t(c.K2 + 0, Y0, Y1, Y2), p1 = dot3_t(c.K2 + 3, Y0, Y1, Y2),
                     p2 = dot3_t(c.K2 + 6, Y0, Y1, Y2);                                           // :67-68
         const float u2 = __fdiv_rn(p0, p2), v2 = __fdiv_rn(p1, p2);
-        const float gx = __fsub_rn(__fdiv_rn(u2, c.half_wm1), 1.0f);                             // :71-73
-        const float gy = __fsub_rn(__fdiv_rn(v2, c.half_hm1), 1.0f);
+        const float gx = __fsub_rn(fastc ? div_const_rn(u2, c.half_wm1, c.rc_wm1) : __fdiv_rn(u2, c.half_wm1), 1.0f);   // :71-73
+        const float gy = __fsub_rn(fastc ? div_const_rn(v2, c.half_hm1, c.rc_hm1) : __fdiv_rn(v2, c.half_hm1), 1.0f);
         const float ix = unnorm(gx, c.half_w), iy = unnorm(gy, c.half_h);                        // :76 (N6)
         const float xw = floorf(ix), yn_ = floorf(iy);
         const float we = __fsub_rn(ix, xw), ee = __fsub_rn(1.0f, we), nn = __fsub_rn(iy, yn_), ss = __fsub_rn(1.0f, nn);
         const int ixw = to_i32(xw), iyn = to_i32(yn_);
-        const int ixe = (ixw == INT_MIN) ? INT_MIN : ixw + 1, iys = (iyn == INT_MIN) ? INT_MIN : iyn + 1;
-        float d12 = __fmul_rn(tap_ds<DS>(sd, H, W, iyn, ixw), __fmul_rn(ss, ee));
-        d12 = __fmaf_rn(tap_ds<DS>(sd, H, W, iyn, ixe), __fmul_rn(ss, we), d12);
-        d12 = __fmaf_rn(tap_ds<DS>(sd, H, W, iys, ixw), __fmul_rn(nn, ee), d12);
-        d12 = __fmaf_rn(tap_ds<DS>(sd, H, W, iys, ixe), __fmul_rn(nn, we), d12);
+        float d12;
+        // all four taps of every lane inside the frame (everything but samples that leave it or touch its border):
+        // no bounds tests, one address, the taps at fixed offsets of it
+        if (__all_sync(0xffffffffu, (unsigned)ixw < (unsigned)(W - 1) && (unsigned)iyn < (unsigned)(H - 1))) {
+            const float *t0 = sd + (size_t)(iyn * W + ixw) * DS, *t1 = t0 + (size_t)W * DS;
+            const float nw = __ldg(t0), ne = __ldg(t0 + DS), sw = __ldg(t1), se = __ldg(t1 + DS);
+            d12 = __fmul_rn(nw, __fmul_rn(ss, ee));
+            d12 = __fmaf_rn(ne, __fmul_rn(ss, we), d12);
+            d12 = __fmaf_rn(sw, __fmul_rn(nn, ee), d12);
+            d12 = __fmaf_rn(se, __fmul_rn(nn, we), d12);
+        } else {
+            const int ixe = (ixw == INT_MIN) ? INT_MIN : ixw + 1, iys = (iyn == INT_MIN) ? INT_MIN : iyn + 1;
+            d12 = __fmul_rn(tap_ds<DS>(sd, H, W, iyn, ixw), __fmul_rn(ss, ee));
+            d12 = __fmaf_rn(tap_ds<DS>(sd, H, W, iyn, ixe), __fmul_rn(ss, we), d12);
+            d12 = __fmaf_rn(tap_ds<DS>(sd, H, W, iys, ixw), __fmul_rn(nn, ee), d12);
+            d12 = __fmaf_rn(tap_ds<DS>(sd, H, W, iys, ixe), __fmul_rn(nn, we), d12);
+        }
         // :79 — (X2 / X2.z) * d12; Y2/Y2 is 1 for finite non-zero Y2 and NaN otherwise
         const float Z0 = __fmul_rn(__fdiv_rn(Y0, Y2), d12), Z1 = __fmul_rn(__fdiv_rn(Y1, Y2), d12);
         const float aY2 = fabsf(Y2);

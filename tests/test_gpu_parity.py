@@ -173,6 +173,22 @@ def test_shared_reciprocal_division_is_ieee():
     assert int(cnt.item()) == 0
 
 
+@pytest.mark.parametrize("size", [1024, 576, 960, 540, 400, 300, 504, 378, 3840, 2160, 128, 96, 131, 97])
+def test_const_division_exhaustive(size):
+    """x / ((size - 1) / 2) of consistency.py:71-73 through the rounded reciprocal (div_const_rn, inverse_kernels.cuh)
+    has the bits of the IEEE division for EVERY finite float x with a normal quotient (all 2^32 patterns tried)."""
+    import ctypes
+    from syn3r_b200 import _native as nat
+    c = np.float32((size - 1) / 2.0)
+    cnt = torch.zeros(2, dtype=torch.int64, device="cuda")      # [mismatches, bit pattern of one failing x]
+    rc = ctypes.c_float(0.0)
+    nat.check(nat.lib().syn3r_selftest_div_const(float(c), 0, 1 << 32, 1, cnt.data_ptr(), ctypes.byref(rc),
+                                                 torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    assert rc.value != 0.0 and abs(rc.value * float(c) - 1.0) < 1e-7
+    assert int(cnt[0].item()) == 0, hex(int(cnt[1].item()))
+
+
 @pytest.mark.parametrize("variant", [{}, {"fp32_tile": True}, {"exact_weight": True}, {"legacy": True}])
 @pytest.mark.parametrize("shape,seed", [((3, 4, 60, 80), 21), ((2, 3, 97, 131), 22), ((1, 2, 16, 8), 23),
                                         ((2, 2, 150, 300), 24)])
