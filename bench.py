@@ -51,7 +51,7 @@ def parse_args():
     ap.add_argument("--gather", default="auto", choices=["auto", "nccl", "peer"],
                     help="N > 1: how finished frames reach rank 0 (auto: direct peer stores when symmetric memory works)")
     ap.add_argument("--gather-chunks", type=int, default=4, help="N > 1, nccl: slot ranges whose send overlaps the next range")
-    ap.add_argument("--wire", default="compact", choices=["compact", "post"],
+    ap.add_argument("--wire", default="compact", choices=["compact", "bytes", "post"],
                     help="N > 1: what travels to rank 0: the reference-facing outputs (uint8 frame + masks + soft mask, 9 B/px) "
                          "or what the SVD pipeline consumes after the post-processing (3.1 B/px)")
     ap.add_argument("--weak", action="store_true", help="N > 1: one whole workload per rank, no collective (secondary figure)")
@@ -361,8 +361,9 @@ def run_ours(args):
     strong = world > 1 and not args.weak
     parts = sharding.partition_units(wl.frames, world) if strong else [(0, wl.frames)] * world
     f0, f1 = parts[rank]
+    packed = strong and args.wire == "compact" and hw % 16 == 0     # the 0/1 masks travel as bits (np.packbits order)
     share = workload.build_plan(wl, f0, f1, seed=(0 if (strong or world == 1) else rank), want_f32=True, want_u8=strong,
-                                want_winner=True)
+                                want_winner=True, pack_masks=packed)
     tw = share.plan
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
@@ -595,15 +596,28 @@ def e2e_single(args, wl, share, timed, mpix_step, big):
         return sh.plan, sh.host_rgbd, sh.host_tgt
 
     e2e_all = None
+    packed = (wl.H * wl.W) % 16 == 0
+    how = (f"TrajectoryWarp.step_host: pinned H2D of RGB-D (+ target depth) on an upload stream, kernels in {args.e2e_chunks} "
+           "slot ranges (uint8 frame + hole mask + winner" + (" + consistency masks" if wl.consistency else "") + "), D2H of "
+           "the outputs the reference's forward_warp / inverse_warp return to their callers, overlapping the next range")
+    if packed:
+        ref_keys = ("rgb_u8", "mask_bits") + (("mask_reproj_bits", "soft_mask_reproj") if wl.consistency else ())
+        p_ref, r_h, t_h = plan_like(want_f32=False, want_u8=True, want_winner=True, host_outputs=ref_keys, pack_masks=True)
+        e2e = measure(p_ref, r_h, t_h, how + "; the two 0/1 masks cross PCIe as bits (np.packbits order, "
+                                             "conditioning.unpack_mask_bits on the host)")
+        assert int(p_ref.out_fwd["status"].max().item()) == 0
+        del p_ref, r_h, t_h
+        torch.cuda.empty_cache()
     ref_keys = ("rgb_u8", "mask") + (("mask_reproj", "soft_mask_reproj") if wl.consistency else ())
     p_ref, r_h, t_h = plan_like(want_f32=False, want_u8=True, want_winner=True, host_outputs=ref_keys)
-    e2e = measure(p_ref, r_h, t_h,
-                  f"TrajectoryWarp.step_host: pinned H2D of RGB-D (+ target depth), kernels in {args.e2e_chunks} slot ranges "
-                  "(uint8 frame + hole mask + winner" + (" + consistency masks" if wl.consistency else "") + "), D2H of the "
-                  "outputs the reference's forward_warp / inverse_warp return to their callers, overlapping the next range")
+    e2e_bytes = measure(p_ref, r_h, t_h, how + "; masks as one byte per pixel")
     assert int(p_ref.out_fwd["status"].max().item()) == 0
     del p_ref, r_h, t_h
     torch.cuda.empty_cache()
+    if packed:
+        e2e["byte_masks"] = {k: e2e_bytes[k] for k in ("value", "ms_per_step", "d2h_bytes_per_step", "host_outputs")}
+    else:
+        e2e = e2e_bytes
     e2e_post, e2e_dropin = None, None
     if wl.H % 8 == 0 and wl.W % 8 == 0 and not big:
         keys = ("post_cond_u8", "post_latent") + (("post_latent_reproj", "post_soft_pooled") if wl.consistency else ())
@@ -669,7 +683,8 @@ def e2e_strong(args, wl, share, parts, timed, mpix_step, dev, rank, world, all_m
         del sh0
     f0, f1 = parts[rank]
     # its own plan with local outputs (the `value` plan may be writing into rank 0's peer buffers)
-    tw = workload.build_plan(wl, f0, f1, seed=0, want_f32=False, want_u8=True, want_winner=True).plan
+    tw = workload.build_plan(wl, f0, f1, seed=0, want_f32=False, want_u8=True, want_winner=True,
+                             pack_masks=(wl.H * wl.W) % 16 == 0).plan
     local_wire = sharding.compact_wire(tw.out_fwd, tw.out_inv)
     counts = [len(workload_slots(wl, a, b)) for a, b in parts]
     pg = sharding.PipelinedGather(local_wire, counts, args.gather_chunks, dst=0)

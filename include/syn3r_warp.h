@@ -177,6 +177,12 @@ int syn3r_points_from_depth(const float *depth, const float *Kinv, int H, int W,
 /* transform_points (consistency.py:25-42): T [16] HOST = pose2 @ inverse(pose1); out = (T [p;1])[:3] / w. */
 int syn3r_transform_points(const float *pts, const float *T, int H, int W, float *out, void *stream);
 
+/* np.packbits(mask != 0) for a device byte mask of n bytes (MSB first; a trailing partial byte is zero-padded):
+ * bits [(n + 7) / 8] u8.  The masks of forward_warp (forward_warp.py:112, mask2) and inverse_warp (:260-267,
+ * mask_reproj) are 0/1 bytes; packed they cross PCIe / NVLink at one bit per pixel and np.unpackbits(bits)[:n]
+ * restores them on the host. */
+int syn3r_pack_mask_bits(const uint8_t *mask, size_t n, uint8_t *bits, void *stream);
+
 /* Caller-side post-processing of P warped frames (model/diffusionGS.py:1572-1597 forward branch, :1452-1491 backward
  * branch), all device pointers, one launch:
  *   hole = 1 - valid -> cv2.dilate 5x5 (outside ignored) -> out_mask_png [P,H,W] 0/255 (the reference's three

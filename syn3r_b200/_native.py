@@ -56,6 +56,7 @@ SIGNATURES = {
     "syn3r_consistency_batched": (c_int, [c_void_p] * 8 + [c_int] * 3 + [c_void_p] * 2),
     "syn3r_points_from_depth": (c_int, [c_void_p] * 2 + [c_int] * 2 + [c_void_p] * 2),
     "syn3r_transform_points": (c_int, [c_void_p] * 2 + [c_int] * 2 + [c_void_p] * 2),
+    "syn3r_pack_mask_bits": (c_int, [c_void_p, c_size_t, c_void_p, c_void_p]),
     "syn3r_condition_post_batched": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p] * 7),
     "syn3r_fuse_uncertainty_batched": (c_int, [c_void_p] * 3 + [c_int] * 3 + [c_void_p] * 4),
     "syn3r_nearby_uncertainty_batched": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_float] + [c_void_p] * 3),

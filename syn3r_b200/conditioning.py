@@ -61,6 +61,30 @@ def condition_post_batched(valid: torch.Tensor, img_u8: Optional[torch.Tensor] =
     return {k: o[k] for k in want}
 
 
+def pack_mask_bits(mask: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """np.packbits(mask != 0) on the device (MSB first): mask [..., n] u8 / bool CUDA, contiguous -> uint8 [(numel + 7) // 8]
+    (flat).  The hole mask of forward_warp and mask_reproj of inverse_warp are 0/1 bytes; packed they cross PCIe / NVLink
+    at one bit per pixel.  `unpack_mask_bits` restores them on the host."""
+    if mask.dtype == torch.bool:
+        mask = mask.view(torch.uint8)
+    assert mask.dtype == torch.uint8 and mask.is_cuda and mask.is_contiguous()
+    n = mask.numel()
+    if out is None:
+        out = torch.empty(((n + 7) // 8,), dtype=torch.uint8, device=mask.device)
+    assert out.dtype == torch.uint8 and out.is_contiguous() and out.numel() == (n + 7) // 8 and out.device == mask.device
+    with torch.cuda.device(mask.device):
+        nat.check(nat.lib().syn3r_pack_mask_bits(nat.ptr(mask), n, nat.ptr(out),
+                                                 torch.cuda.current_stream(mask.device).cuda_stream), "syn3r_pack_mask_bits")
+    return out
+
+
+def unpack_mask_bits(bits, shape) -> np.ndarray:
+    """Host side of pack_mask_bits: uint8 bit array (NumPy or CPU tensor) -> bool array of `shape`."""
+    b = bits.numpy() if isinstance(bits, torch.Tensor) else np.asarray(bits)
+    n = int(np.prod(shape))
+    return np.unpackbits(b.reshape(-1), count=n).astype(bool).reshape(shape)
+
+
 def _dev():
     if not torch.cuda.is_available():
         raise nat.Syn3rNativeError("syn3r_b200.conditioning needs a CUDA device; there is no CPU path")

@@ -159,7 +159,7 @@ static int launch_tile_fx_as(const TileArgs &ta, int n_items, cudaStream_t st) {
                                             (int)smem_redo));
         configured_dev = dev;
     }
-    int grid = sm_count();
+    int grid = sm_count() * (SYN3R_FX_TWO_CTAS ? 2 : 1);
     if (grid > n_items) grid = n_items;
     k_fwd_tile_fx<WINNER, FLAT><<<grid, SYN3R_TILE_THREADS, smem, st>>>(ta);
     TileArgs tr = ta;

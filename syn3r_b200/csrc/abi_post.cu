@@ -27,6 +27,26 @@ int syn3r_condition_post_batched(const uint8_t *valid, const uint8_t *img_u8, co
     return check_cuda(cudaGetLastError(), "k_condition_post");
 }
 
+int syn3r_pack_mask_bits(const uint8_t *mask, size_t n, uint8_t *bits, void *stream) {
+    if (n == 0) return SYN3R_OK;
+    SYN3R_REQUIRE(mask && bits, "null required pointer");
+    int rc = check_device();
+    if (rc != SYN3R_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    size_t n16 = (((uintptr_t)mask & 15) == 0 && ((uintptr_t)bits & 1) == 0) ? n / 16 : 0;
+    if (n16) {
+        size_t blocks = (n16 + 255) / 256, cap = (size_t)sm_count() * 16;
+        k_pack_mask_bits<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, st>>>(reinterpret_cast<const uint4 *>(mask), n16,
+                                                                               reinterpret_cast<unsigned short *>(bits));
+    }
+    const size_t first = n16 * 16;
+    if (first < n) {
+        const size_t out_bytes = (n - first + 7) / 8;
+        k_pack_mask_bits_tail<<<(unsigned)((out_bytes + 255) / 256), 256, 0, st>>>(mask, first, n, bits);
+    }
+    return check_cuda(cudaGetLastError(), "k_pack_mask_bits");
+}
+
 int syn3r_fuse_uncertainty_batched(const float *cond_ori, const float *gs, const float *soft_ori, int N, int H, int W,
                                    float *out_cond, float *out_masks, double *out_unc, void *stream) {
     if (N == 0) return SYN3R_OK;

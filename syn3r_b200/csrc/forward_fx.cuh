@@ -40,6 +40,11 @@ namespace syn3r {
 #define SYN3R_FX_UNITS (SYN3R_BLK_H / SYN3R_FX_UNIT_ROWS)
 #define SYN3R_FX_FLAT 2304    /* FLAT kernels: frames of up to this many source blocks (a 1024 x 576 frame), culled in one
                                  pass; listB holds them all */
+#if SYN3R_FX_TWO_CTAS
+#define SYN3R_FX_LISTB_CAP 1024     /* A/B build only: hits of one 128 x 24 tile (no overflow guard) */
+#else
+#define SYN3R_FX_LISTB_CAP SYN3R_FX_FLAT
+#endif
 #define SYN3R_FX_FLAT_PER_THREAD ((SYN3R_FX_FLAT + SYN3R_TILE_THREADS - 1) / SYN3R_TILE_THREADS)
 // Floor experiments (timing builds only, results are WRONG for every value but 0):
 //   1  sweep 2 skipped            2  sweep 2 with an fp32 projection, no exactness filter, approximate weight (what a
@@ -461,7 +466,8 @@ __device__ __forceinline__ void fx_stream(const TileArgs &a, const FxAux &sm, co
 
 __host__ __device__ inline size_t fx_smem_bytes(bool winner) {
     const size_t cells = (size_t)SYN3R_TILE_W * SYN3R_TILE_H;
-    return (cells + SYN3R_TILE_W) * 4 * (winner ? 8 : 6) + (size_t)SYN3R_LOGTAB * 16 + (SYN3R_LISTA + SYN3R_FX_FLAT) * 4 + 64;
+    return (cells + SYN3R_TILE_W) * 4 * (winner ? 8 : 6) + (SYN3R_FX_TWO_CTAS ? 0 : (size_t)SYN3R_LOGTAB * 16) +
+           (SYN3R_LISTA + SYN3R_FX_LISTB_CAP) * 4 + 64;
 }
 
 // culls the pair's source blocks against the tile and runs one sweep over the survivors.
@@ -574,15 +580,22 @@ __device__ __forceinline__ unsigned u8_round(float v) {      // clip + round-hal
     return (unsigned)__float2int_rn(fminf(fmaxf(v, 0.0f), 255.0f));
 }
 
+#if SYN3R_FX_TWO_CTAS
+__device__ double2 g_fx_logtab[SYN3R_LOGTAB];
+#endif
 template <bool WINNER, bool FLAT>
-__global__ void __launch_bounds__(SYN3R_TILE_THREADS, 1)
+__global__ void __launch_bounds__(SYN3R_TILE_THREADS, SYN3R_FX_TWO_CTAS ? 2 : 1)
 k_fwd_tile_fx(const TileArgs a) {
     const int CELLS = FX_PLANE, NPL = WINNER ? 8 : 6;          // plane stride incl. the trash row
     FxAux sm;
     unsigned char *ptr = reinterpret_cast<unsigned char *>(fx_smem + NPL * CELLS);
+#if SYN3R_FX_TWO_CTAS
+    sm.logtab = g_fx_logtab;                                   // A/B build: the table lives in global memory (L1)
+#else
     sm.logtab = reinterpret_cast<double2 *>(ptr); ptr += (size_t)SYN3R_LOGTAB * 16;
+#endif
     sm.listA = reinterpret_cast<int *>(ptr); ptr += SYN3R_LISTA * 4;
-    sm.listB = reinterpret_cast<int *>(ptr); ptr += SYN3R_FX_FLAT * 4;
+    sm.listB = reinterpret_cast<int *>(ptr); ptr += SYN3R_FX_LISTB_CAP * 4;
     sm.ctl = reinterpret_cast<int *>(ptr);
     int *ctl = sm.ctl;
 

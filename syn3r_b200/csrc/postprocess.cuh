@@ -343,4 +343,38 @@ k_nearby_uncertainty(const float *__restrict__ soft, const float *__restrict__ w
     if (out_int) nb_store<VEC>(out_int + (size_t)n * hw + i, v);
 }
 
+// ---------------------------------------------------------------------------------------------
+// k_pack_mask_bits: np.packbits of a 0/1 byte mask (MSB first, the NumPy default), so that a mask travels over PCIe /
+// NVLink at 1 bit per pixel instead of 8.  One thread: 16 mask bytes (one 16-byte load) -> 2 bytes; a warp reads 512
+// contiguous bytes and writes 64.  Bytes are tested `!= 0` like astype(bool).  n = number of mask bytes, a multiple
+// of 16 (the launcher handles the tail with the byte-wise kernel).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned pack8_msb_first(unsigned lo, unsigned hi) {
+    // lo = mask bytes 0..3 (byte 0 in the low bits), hi = bytes 4..7 -> bit 7 = byte 0 ... bit 0 = byte 7
+    unsigned r = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        r |= ((lo >> (8 * k)) & 0xffu) ? (0x80u >> k) : 0u;
+        r |= ((hi >> (8 * k)) & 0xffu) ? (0x08u >> k) : 0u;
+    }
+    return r;
+}
+__global__ void __launch_bounds__(256)
+k_pack_mask_bits(const uint4 *__restrict__ mask, size_t n16, unsigned short *__restrict__ bits) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) {
+        const uint4 v = ld_stream_u4(mask + i);
+        bits[i] = (unsigned short)(pack8_msb_first(v.x, v.y) | (pack8_msb_first(v.z, v.w) << 8));
+    }
+}
+__global__ void __launch_bounds__(256)
+k_pack_mask_bits_tail(const uint8_t *__restrict__ mask, size_t first, size_t n, uint8_t *__restrict__ bits) {
+    // output bytes first / 8 ... ; a trailing partial byte is zero-padded like np.packbits
+    const size_t b = first / 8 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b * 8 >= n) return;
+    unsigned r = 0;
+    for (int k = 0; k < 8; ++k)
+        if (b * 8 + k < n && mask[b * 8 + k]) r |= 0x80u >> k;
+    bits[b] = (uint8_t)r;
+}
+
 }  // namespace syn3r

@@ -61,16 +61,23 @@ def pairs_for_frames(S: int, t0: int, t1: int, policy: str = "all"):
 
 def compact_wire(out_fwd: Dict[str, torch.Tensor], out_inv: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
     """The tensors the diffusion rank consumes: uint8 warped colour, hole mask, reprojection mask (+ the soft
-    mask when present).  Leading axis = the rank's own units (pairs)."""
+    mask when present).  Leading axis = the rank's own units (pairs).  A plan built with pack_masks=True ships the two
+    0/1 masks as bits (`mask_bits`, `mask_reproj_bits`: np.packbits order, 1 bit per pixel instead of 8)."""
     wire = {}
     if "rgb_u8" in out_fwd:
         wire["rgb_u8"] = out_fwd["rgb_u8"]
     elif "rgb_f32" in out_fwd:
         wire["rgb_f32"] = out_fwd["rgb_f32"]
-    wire["mask"] = out_fwd["mask"]
-    for k in ("mask_reproj", "soft_mask_reproj"):
-        if k in out_inv:
-            wire[k] = out_inv[k]
+    if "mask_bits" in out_fwd:
+        wire["mask_bits"] = out_fwd["mask_bits"]
+    else:
+        wire["mask"] = out_fwd["mask"]
+    if "mask_reproj_bits" in out_inv:
+        wire["mask_reproj_bits"] = out_inv["mask_reproj_bits"]
+    elif "mask_reproj" in out_inv:
+        wire["mask_reproj"] = out_inv["mask_reproj"]
+    if "soft_mask_reproj" in out_inv:
+        wire["soft_mask_reproj"] = out_inv["soft_mask_reproj"]
     return wire
 
 

@@ -36,7 +36,8 @@ class TrajectoryWarp:
     def __init__(self, S: int, T: int, H: int, W: int, pair_src: Sequence[int], pair_tgt: Sequence[int], *,
                  device=None, consistency: bool = True, want_f32: bool = True, want_u8: bool = False,
                  want_winner: bool = True, bandwidth: float = 20.0, pinned_host: bool = False,
-                 host_outputs: Optional[Sequence[str]] = None, post: bool = False, fused: bool = False):
+                 host_outputs: Optional[Sequence[str]] = None, post: bool = False, fused: bool = False,
+                 pack_masks: bool = False):
         """fused=True (extension): the pairs of a target frame share ONE accumulator, outputs are per target frame
         ([T,H,W,...]); the pairs must be ordered by target (synth.target_major) and there is no per-pair consistency pass."""
         self.S, self.T, self.H, self.W = S, T, H, W
@@ -75,6 +76,13 @@ class TrajectoryWarp:
         if consistency:
             self.out_inv["mask_reproj"] = torch.empty((P, H, W), dtype=torch.uint8, device=d)
             self.out_inv["soft_mask_reproj"] = torch.empty((P, H, W), dtype=torch.float32, device=d)
+        # bit-packed copies of the 0/1 masks (np.packbits order) for the trips over PCIe / NVLink: 1 bit per pixel
+        self.pack_masks = bool(pack_masks)
+        if self.pack_masks:
+            assert (H * W) % 16 == 0, "pack_masks needs H * W to be a multiple of 16 (whole bytes per slot, aligned loads)"
+            self.out_fwd["mask_bits"] = torch.empty((P, H * W // 8), dtype=torch.uint8, device=d)
+            if consistency:
+                self.out_inv["mask_reproj_bits"] = torch.empty((P, H * W // 8), dtype=torch.uint8, device=d)
         # the callers' per-frame post-processing (diffusionGS.py:1572-1597, :1452-1491) as part of every run
         self.post = bool(post)
         self.out_post = {}
@@ -194,15 +202,26 @@ class TrajectoryWarp:
                                 self.pair_tgt[sl], rgbd=self.rgbd, bandwidth=self.bandwidth,
                                 want=("mask_reproj", "soft_mask_reproj"), out=out_i)
 
-    def _run_range(self, p0: int, p1: int):
-        """Forward warp (+ consistency masks) of output slots [p0, p1) (pairs; target frames in FUSED mode) into the
-        matching slices of the outputs."""
-        sl = slice(None) if (p0 == 0 and p1 == self.N) else slice(p0, p1)
-        if not self.consistency:
-            self._forward(sl)
+    def _pack(self, sl, fwd: bool):
+        from . import conditioning as _c
+        if fwd:
+            _c.pack_mask_bits(self.out_fwd["mask"][sl], out=self.out_fwd["mask_bits"][sl].view(-1))
         else:
-            self._forward(sl)
+            _c.pack_mask_bits(self.out_inv["mask_reproj"][sl], out=self.out_inv["mask_reproj_bits"][sl].view(-1))
+
+    def _run_range(self, p0: int, p1: int, before_inverse=None):
+        """Forward warp (+ consistency masks) of output slots [p0, p1) (pairs; target frames in FUSED mode) into the
+        matching slices of the outputs.  `before_inverse()` runs between the two (step_host: wait for the target depth)."""
+        sl = slice(None) if (p0 == 0 and p1 == self.N) else slice(p0, p1)
+        self._forward(sl)
+        if self.pack_masks:
+            self._pack(slice(p0, p1), True)
+        if self.consistency:
+            if before_inverse is not None:
+                before_inverse()
             self._inverse(sl)
+            if self.pack_masks:
+                self._pack(slice(p0, p1), False)
         if self.post:
             self._post(sl)
 
@@ -237,24 +256,35 @@ class TrajectoryWarp:
         cur = torch.cuda.current_stream()
         if getattr(self, "_copy_stream", None) is None:
             self._copy_stream = torch.cuda.Stream(device=self.dev)
-        side = self._copy_stream
-        # inputs: the sources first (every pair needs them); a target's depth map only right before the first pair
-        # range that reads it, so that with target-major pairs the first range starts after S + a few maps, not all
-        self.rgbd.copy_(rgbd_host, non_blocking=True)
-        sent = np.zeros(self.T, bool)
+            self._up_stream = torch.cuda.Stream(device=self.dev)
+        side, up = self._copy_stream, self._up_stream
+        # inputs travel on their own stream: the sources first (the forward kernels need nothing else), then the
+        # target depth maps in the order the slot ranges read them.  Only the consistency kernel of a range waits for
+        # its maps, so the upload of range c + 1 overlaps the kernels of range c instead of sitting in front of them.
+        up.wait_stream(cur)
         n = max(1, min(int(chunks), self.N))
         bounds = [(self.N * c) // n for c in range(n + 1)]
+        ev_src, ev_tgt = torch.cuda.Event(), []
+        with torch.cuda.stream(up):
+            self.rgbd.copy_(rgbd_host, non_blocking=True)
+            ev_src.record(up)
+            sent = np.zeros(self.T, bool)
+            for c in range(n):
+                if self.consistency:
+                    need = np.unique(self.pair_tgt_h[bounds[c]:bounds[c + 1]])
+                    need = need[~sent[need]]
+                    sent[need] = True
+                    # contiguous runs of target indices -> one copy each
+                    for run in np.split(need, np.nonzero(np.diff(need) != 1)[0] + 1) if need.size else []:
+                        a, b = int(run[0]), int(run[-1]) + 1
+                        self.tgt_depth[a:b].copy_(tgt_depth_host[a:b], non_blocking=True)
+                e = torch.cuda.Event()
+                e.record(up)
+                ev_tgt.append(e)
+        cur.wait_event(ev_src)
         for c in range(n):
             p0, p1 = bounds[c], bounds[c + 1]
-            if self.consistency:
-                need = np.unique(self.pair_tgt_h[p0:p1])
-                need = need[~sent[need]]
-                sent[need] = True
-                # contiguous runs of target indices -> one copy each
-                for run in np.split(need, np.nonzero(np.diff(need) != 1)[0] + 1) if need.size else []:
-                    a, b = int(run[0]), int(run[-1]) + 1
-                    self.tgt_depth[a:b].copy_(tgt_depth_host[a:b], non_blocking=True)
-            self._run_range(p0, p1)
+            self._run_range(p0, p1, before_inverse=lambda c=c: cur.wait_event(ev_tgt[c]))
             ev = torch.cuda.Event()
             ev.record(cur)
             side.wait_event(ev)
@@ -262,12 +292,14 @@ class TrajectoryWarp:
                 for k, v in self._host_items():
                     self.pinned["out_" + k][p0:p1].copy_(v[p0:p1], non_blocking=True)
         cur.wait_stream(side)
+        cur.wait_stream(up)
         return self.pinned
 
     def launches_per_run(self) -> int:
         """Kernels of libsyn3r_warp.so per run() (memsets not counted): k_src_stats, k_fwd_prep (bounds), k_fwd_prep (pruned max z'),
         k_fwd_finalize, k_fwd_tile_fx, k_fwd_tile (redo list, normally empty) (+ k_reproj_masks)."""
-        return 6 + (1 if self.consistency else 0) + ((2 if self.consistency else 1) if self.post else 0)
+        return (6 + (1 if self.consistency else 0) + ((2 if self.consistency else 1) if self.post else 0) +
+                ((2 if self.consistency else 1) if self.pack_masks else 0))
 
 
 def from_synth(traj, pairs=None, **kw) -> TrajectoryWarp:

@@ -43,6 +43,9 @@ def redo_items(device) -> int:
     """Work items ((slot, tile) pairs) the integer tile kernel handed to the fp32 kernel in the LAST forward call on
     `device` (crowded cells, NaN-poisoned pairs, non-finite colours; normally 0).  Reads the redo counter of the call's
     workspace (abi.cu fwd_layout: counter block behind the per-pair max-z' keys and NaN flags); synchronises."""
+    device = torch.device(device)
+    if device.index is None:                               # "cuda" -> the current device, like torch itself
+        device = torch.device("cuda", torch.cuda.current_device())
     ent = _last_fwd.get(str(device))
     if ent is None:
         return 0

@@ -236,6 +236,32 @@ def test_crowded_cells_take_redo_path():
         _check_slot(o, p, r)
 
 
+@pytest.mark.parametrize("pull_back,expect_redo", [(1.5, 0), (2.0, 3), (5.5, None)])
+def test_many_fused_sources_under_minification(pull_back, expect_redo):
+    """Config-E style crowding: 16 sources FUSED into a target camera pulled back along its optical axis, so that a
+    cell receives ~ 4 S m^2 corner updates (m = minification).  Past FX_MAX_N = 512 updates a work item goes through
+    the redo list to the fp32 tile kernel; below it the integer kernel handles all 16 sources.  pull_back 1.5: up to
+    420 updates per cell, no item redone; 2.0: 3 of the 6 tiles hold a cell past 512 (565 / 567 / 599 updates, counted
+    on the host with the reference's floor / ceil corners); 5.5: every tile that is touched.  All must agree with the
+    oracle; the number of redone items is printed."""
+    from syn3r_b200 import warp as w
+    S, T, H, W = 16, 1, 144, 256
+    tr = synth.make_trajectory(S, T, H, W, seed=61, pose_step=0.25)
+    tr.pose_tgt[:, 2, 3] += pull_back                  # w2c translation along the optical axis
+    ps, pt = synth.all_pairs(S, T)
+    o = _run_pairs(tr, ps, pt, fused=True)
+    redo = w.redo_items(torch.device("cuda"))
+    n_items = T * ((W + 127) // 128) * ((H + 47) // 48)
+    print(f"pull_back {pull_back}: {redo} of {n_items} work items took the fp32 redo kernel")
+    r = _oracle_pair(tr, list(range(S)), 0)
+    assert r["mask"].sum() > 500
+    _check_slot(o, 0, r)
+    if expect_redo is not None:
+        assert redo == expect_redo
+    else:
+        assert redo > 0
+
+
 def test_large_frame_takes_two_level_cull():
     """1088 x 576 = 2880 source-block slots > SYN3R_FX_FLAT (2304): the integer tile kernel is launched without the
     one-pass cull (abi.cu launch_tile_fx) and goes through the super-block / block lists; pair and fused mode."""

@@ -193,3 +193,49 @@ def test_nearby_uncertainty_kernel_vs_oracle(N, H, W, radius):
 def test_nearby_uncertainty_empty_is_a_no_op():
     from syn3r_b200 import _native as nat
     assert nat.lib().syn3r_nearby_uncertainty_batched(None, None, None, None, 0, 8, 8, 10.0, None, None, None) == 0
+
+
+@pytest.mark.parametrize("n", [16, 17, 31, 4096, 4096 + 5, 576 * 1024, 300 * 400 * 3 + 7])
+def test_pack_mask_bits_is_np_packbits(n):
+    """syn3r_pack_mask_bits == np.packbits(mask != 0) (MSB first, zero-padded tail), aligned and unaligned starts."""
+    from syn3r_b200 import conditioning as c
+    rng = np.random.default_rng(n)
+    m = (rng.random(n + 3) < 0.4).astype(np.uint8) * rng.integers(1, 256, n + 3).astype(np.uint8)   # any non-zero byte is True
+    for off in (0, 3):                                   # off = 3: a 16-byte-misaligned start takes the byte-wise kernel
+        t = torch.from_numpy(m).cuda()[off:off + n].contiguous() if off == 0 else torch.from_numpy(m).cuda()[off:off + n]
+        bits = c.pack_mask_bits(t if t.is_contiguous() else t.contiguous())
+        ref = np.packbits(m[off:off + n] != 0)
+        assert np.array_equal(bits.cpu().numpy(), ref)
+        assert np.array_equal(c.unpack_mask_bits(bits.cpu(), (n,)), m[off:off + n] != 0)
+
+
+def test_trajectory_packed_masks_and_step_host_match_run():
+    """pack_masks=True: the bit planes are np.packbits of the byte masks per slot; step_host (upload stream, slot ranges,
+    D2H on a side stream) delivers exactly what run() leaves on the device."""
+    from syn3r_b200 import synth, trajectory, warp as w
+    S, T, H, W = 2, 5, 64, 96
+    tr = synth.make_trajectory(S, T, H, W, seed=11)
+    ps, pt = synth.target_major(*synth.all_pairs(S, T))
+    keys = ("rgb_u8", "mask_bits", "mask_reproj_bits", "soft_mask_reproj")
+    tw = trajectory.from_synth(tr, pairs=(ps, pt), want_f32=False, want_u8=True, want_winner=True, pack_masks=True,
+                               pinned_host=True, host_outputs=keys)
+    rgbd_h = torch.from_numpy(w.pack_rgbd(tr.rgb, tr.depth)).pin_memory()
+    tgt_h = torch.from_numpy(tr.depth_tgt).pin_memory()
+    tw.upload(rgbd_h, tgt_h)
+    o = tw.run()
+    torch.cuda.synchronize()
+    mb = tw.out_fwd["mask_bits"].cpu().numpy()
+    rb = tw.out_inv["mask_reproj_bits"].cpu().numpy()
+    for p in range(tw.P):
+        assert np.array_equal(mb[p], np.packbits(o.mask[p].cpu().numpy().reshape(-1) != 0))
+        assert np.array_equal(rb[p], np.packbits(o.mask_reproj[p].cpu().numpy().reshape(-1) != 0))
+    ref = {k: v.clone() for k, v in {**tw.out_fwd, **tw.out_inv}.items()}
+    for d in (tw.out_fwd, tw.out_inv):
+        for v in d.values():
+            v.zero_()
+    tw.rgbd.zero_()
+    tw.tgt_depth.zero_()
+    pinned = tw.step_host(rgbd_h, tgt_h, chunks=3)
+    torch.cuda.synchronize()
+    for k in keys:
+        assert torch.equal(pinned["out_" + k], ref[k].cpu()), k
