@@ -33,13 +33,13 @@ int syn3r_pack_mask_bits(const uint8_t *mask, size_t n, uint8_t *bits, void *str
     int rc = check_device();
     if (rc != SYN3R_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    size_t n16 = (((uintptr_t)mask & 15) == 0 && ((uintptr_t)bits & 1) == 0) ? n / 16 : 0;
-    if (n16) {
-        size_t blocks = (n16 + 255) / 256, cap = (size_t)sm_count() * 16;
-        k_pack_mask_bits<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, st>>>(reinterpret_cast<const uint4 *>(mask), n16,
-                                                                               reinterpret_cast<unsigned short *>(bits));
+    size_t n32 = (((uintptr_t)mask & 15) == 0 && ((uintptr_t)bits & 3) == 0) ? n / 32 : 0;
+    if (n32) {
+        size_t blocks = (n32 + 255) / 256, cap = (size_t)sm_count() * 16;
+        k_pack_mask_bits<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, st>>>(reinterpret_cast<const uint4 *>(mask), n32,
+                                                                               reinterpret_cast<unsigned *>(bits));
     }
-    const size_t first = n16 * 16;
+    const size_t first = n32 * 32;
     if (first < n) {
         const size_t out_bytes = (n - first + 7) / 8;
         k_pack_mask_bits_tail<<<(unsigned)((out_bytes + 255) / 256), 256, 0, st>>>(mask, first, n, bits);

@@ -701,6 +701,7 @@ k_fwd_tile_fx(const TileArgs a) {
         bool bad = false;
         const int tw = tx1 - tx0 + 1, th = ty1 - ty0 + 1;
         const bool vec = (tw == SYN3R_TILE_W) && ((W & 3) == 0);
+        const bool u8_wide = vec && ((W & 15) == 0) && ((hw & 15u) == 0u) && ((reinterpret_cast<uintptr_t>(a.out_u8) & 15) == 0);
 #if SYN3R_FX_TRASH_SPLIT
         // the trash row (row TILE_H, cleared only) is shared out over all threads: with it in the row loop one warp of
         // 24 would make a third trip for 49 rows
@@ -746,13 +747,31 @@ k_fwd_tile_fx(const TileArgs a) {
                     st_once_f4(f + 2, make_float4(o[2].v2, o[3].v0, o[3].v1, o[3].v2), once);
                 }
                 if (a.out_u8) {
-                    unsigned b[12];
+                    unsigned b[12], wd[3];
 #pragma unroll
                     for (int j = 0; j < 4; ++j) { b[3 * j] = u8_round(o[j].v0); b[3 * j + 1] = u8_round(o[j].v1); b[3 * j + 2] = u8_round(o[j].v2); }
-                    unsigned *u = reinterpret_cast<unsigned *>(a.out_u8 + q * 3);
 #pragma unroll
-                    for (int k = 0; k < 3; ++k)
-                        st_once_u32(u + k, b[4 * k] | (b[4 * k + 1] << 8) | (b[4 * k + 2] << 16) | (b[4 * k + 3] << 24), once);
+                    for (int k = 0; k < 3; ++k) wd[k] = b[4 * k] | (b[4 * k + 1] << 8) | (b[4 * k + 2] << 16) | (b[4 * k + 3] << 24);
+                    if (u8_wide) {
+                        // the row's 384 bytes leave as 24 x 16-byte stores, whole 128-byte lines (one third of the store
+                        // instructions and, when out_u8 is a peer's memory, whole NVLink write packets instead of 4 bytes
+                        // every 12): staged through this row of the I0 plane, which was read and cleared above
+                        unsigned *stage = fx_smem + FX_I0 * CELLS + ly * SYN3R_TILE_W;
+#pragma unroll
+                        for (int k = 0; k < 3; ++k) stage[3 * lane + k] = wd[k];
+                        __syncwarp();
+                        if (lane < 24) {
+                            const uint4 v = *reinterpret_cast<const uint4 *>(stage + 4 * lane);
+                            *reinterpret_cast<uint4 *>(stage + 4 * lane) = make_uint4(0u, 0u, 0u, 0u);
+                            st_once_i4(reinterpret_cast<int4 *>(a.out_u8 + (q - (size_t)(lane * 4)) * 3) + lane,
+                                       make_int4((int)v.x, (int)v.y, (int)v.z, (int)v.w), once);
+                        }
+                        __syncwarp();
+                    } else {
+                        unsigned *u = reinterpret_cast<unsigned *>(a.out_u8 + q * 3);
+#pragma unroll
+                        for (int k = 0; k < 3; ++k) st_once_u32(u + k, wd[k], once);
+                    }
                 }
                 if (WINNER && a.out_winner)
                     st_once_i4(reinterpret_cast<int4 *>(a.out_winner + q), make_int4(o[0].win, o[1].win, o[2].win, o[3].win), once);

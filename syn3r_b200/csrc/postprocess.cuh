@@ -345,9 +345,9 @@ k_nearby_uncertainty(const float *__restrict__ soft, const float *__restrict__ w
 
 // ---------------------------------------------------------------------------------------------
 // k_pack_mask_bits: np.packbits of a 0/1 byte mask (MSB first, the NumPy default), so that a mask travels over PCIe /
-// NVLink at 1 bit per pixel instead of 8.  One thread: 16 mask bytes (one 16-byte load) -> 2 bytes; a warp reads 512
-// contiguous bytes and writes 64.  Bytes are tested `!= 0` like astype(bool).  n = number of mask bytes, a multiple
-// of 16 (the launcher handles the tail with the byte-wise kernel).
+// NVLink at 1 bit per pixel instead of 8.  One thread: 32 mask bytes -> 4 bytes; a warp reads 1 KB and writes one
+// 128-byte line.  Bytes are tested `!= 0` like astype(bool).  The launcher handles a tail that is not a multiple of
+// 32 bytes (and misaligned pointers) with the byte-wise kernel.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned pack8_msb_first(unsigned lo, unsigned hi) {
     // lo = mask bytes 0..3 (byte 0 in the low bits), hi = bytes 4..7 -> bit 7 = byte 0 ... bit 0 = byte 7
@@ -360,10 +360,12 @@ __device__ __forceinline__ unsigned pack8_msb_first(unsigned lo, unsigned hi) {
     return r;
 }
 __global__ void __launch_bounds__(256)
-k_pack_mask_bits(const uint4 *__restrict__ mask, size_t n16, unsigned short *__restrict__ bits) {
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) {
-        const uint4 v = ld_stream_u4(mask + i);
-        bits[i] = (unsigned short)(pack8_msb_first(v.x, v.y) | (pack8_msb_first(v.z, v.w) << 8));
+k_pack_mask_bits(const uint4 *__restrict__ mask, size_t n32, unsigned *__restrict__ bits) {
+    // one thread: 32 mask bytes (two 16-byte loads) -> one 32-bit word; a warp writes one whole 128-byte line
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n32; i += (size_t)gridDim.x * blockDim.x) {
+        const uint4 v = ld_stream_u4(mask + 2 * i), w = ld_stream_u4(mask + 2 * i + 1);
+        bits[i] = pack8_msb_first(v.x, v.y) | (pack8_msb_first(v.z, v.w) << 8) | (pack8_msb_first(w.x, w.y) << 16) |
+                  (pack8_msb_first(w.z, w.w) << 24);
     }
 }
 __global__ void __launch_bounds__(256)
