@@ -105,7 +105,7 @@ def forward_pair_params(T_src, T_tgt, K_src, K_tgt, pair_src, pair_tgt):
 def forward_warp_batched(rgbd, Kinv_src, pair_par, pair_src, *, pair_slot=None, n_slots=None, depth64=None,
                          src_mask=None, want_f32=True, want_u8=True, want_winner=False, want_flow=False,
                          gate06=False, is_image=True, out=None, phases=0, exact_weight=False, legacy=False,
-                         fp32_tile=False):
+                         fp32_tile=False, workspace=None):
     """Launch the forward warp for P pairs.  All array arguments are CUDA tensors:
     rgbd [S,H,W,4] f32, Kinv_src [S,9] f64, pair_par [P,24] f64, pair_src [P] i32,
     pair_slot [P] i32 or None (PAIR mode).  Returns a dict of CUDA tensors
@@ -113,7 +113,10 @@ def forward_warp_batched(rgbd, Kinv_src, pair_par, pair_src, *, pair_slot=None, 
     status [n] i32).  `out` may carry preallocated tensors under the same keys.
     `exact_weight`: IEEE log/exp/div for the soft depth weight (default: fast fp64 table path, rel. err < 3e-7);
     `legacy`: first-generation global-accumulator kernels, `fp32_tile`: second-generation per-tile fp32
-    accumulators (A/B measurements; default is the integer block-floating-point tile kernel)."""
+    accumulators (A/B measurements; default is the integer block-floating-point tile kernel).
+    `workspace`: a caller-owned uint8 CUDA tensor of at least `fwd_workspace_bytes` (a holder: `workspace[0]` is
+    replaced when it has to grow); default: one cached per (device, stream).  A caller that runs the phases of one
+    call on two streams (TrajectoryWarp) must own it."""
     L = nat.lib()
     S, H, W, four = rgbd.shape
     assert four == 4 and rgbd.dtype == torch.float32
@@ -142,7 +145,12 @@ def forward_warp_batched(rgbd, Kinv_src, pair_par, pair_src, *, pair_slot=None, 
     flow = get("flow", want_flow, (P, H, W, 2), torch.float64)
     status = get("status", True, (n,), torch.int32)
     nbytes = L.syn3r_fwd_workspace_bytes(H, W, S, P, n, flags)
-    ws = _workspace(nbytes, dev, "fwd")
+    if workspace is not None:
+        if workspace[0] is None or workspace[0].numel() < nbytes:
+            workspace[0] = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=dev)
+        ws = workspace[0]
+    else:
+        ws = _workspace(nbytes, dev, "fwd")
     _last_fwd[str(dev)] = (ws, P)
     with torch.cuda.device(dev):        # the C side sizes its grid from, and launches on, the CURRENT device
         rc = L.syn3r_forward_warp_batched(
