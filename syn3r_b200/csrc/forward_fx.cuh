@@ -423,10 +423,17 @@ __device__ __forceinline__ void fx_stream(const TileArgs &a, const FxAux &sm, co
     const float4 *frame = a.rgbd + (size_t)s * (size_t)(H * W);
     const unsigned ibase = (unsigned)s * (unsigned)(H * W);
     const double tx1d = (double)(tx0 - 1), ty1d = (double)(ty0 - 1);
-    int kraw = 0;
-    if (lane == 0) kraw = atomicAdd(ctr, 1);
+    // lane 0 claims for the warp: a plain atom.shared (the compiler would wrap atomicAdd() in its own warp-aggregation
+    // sequence of a dozen instructions, pointless with one active lane)
+    const unsigned ctr_s = (unsigned)__cvta_generic_to_shared(ctr);
+    auto claim = [&]() {
+        int v = 0;
+        if (lane == 0) asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(v) : "r"(ctr_s) : "memory");
+        return v;
+    };
+    int kraw = claim();
     int k = __shfl_sync(0xffffffffu, kraw, 0);
-    if (lane == 0) kraw = atomicAdd(ctr, 1);                    // the claim after that: consumed one iteration later
+    kraw = claim();                                             // the claim after that: consumed one iteration later
     if (k >= total) return;
     int x, y;
     float4 pxa, pxb;
@@ -441,7 +448,7 @@ __device__ __forceinline__ void fx_stream(const TileArgs &a, const FxAux &sm, co
     fetch(k);
     for (;;) {
         const int kn = __shfl_sync(0xffffffffu, kraw, 0);
-        if (lane == 0) kraw = atomicAdd(ctr, 1);
+        kraw = claim();
         const float4 px[2] = {pxa, pxb};
         const int cx = x, cy = y;
         if (kn < total) fetch(kn);
