@@ -359,7 +359,8 @@ def run_ours(args):
     H, W, hw = wl.H, wl.W, wl.H * wl.W
     big = wl.lazy_sources                                         # config E: GBs of inputs / outputs per rank
     strong = world > 1 and not args.weak
-    parts = sharding.partition_units(wl.frames, world) if strong else [(0, wl.frames)] * world
+    # strong scaling: rank 0 (the diffusion rank) also ingests every peer's stores, so it gets a light share
+    parts = sharding.partition_units(wl.frames, world, light=0) if strong else [(0, wl.frames)] * world
     f0, f1 = parts[rank]
     packed = strong and args.wire == "compact" and hw % 16 == 0     # the 0/1 masks travel as bits (np.packbits order)
     share = workload.build_plan(wl, f0, f1, seed=(0 if (strong or world == 1) else rank), want_f32=True, want_u8=strong,

@@ -24,14 +24,21 @@ import torch
 import torch.distributed as dist
 
 
-def partition_units(n: int, world: int) -> List[Tuple[int, int]]:
+def partition_units(n: int, world: int, light: int = None) -> List[Tuple[int, int]]:
     """Contiguous block partition of n independent units over `world` ranks: [(begin, end)] per rank; the first
-    n % world ranks get one more (100 frames over 8 GPUs -> 13,13,13,13,12,12,12,12)."""
+    n % world ranks get one more (100 frames over 8 GPUs -> 13,13,13,13,12,12,12,12).
+    `light` = a rank that should carry a small share - the diffusion rank, whose HBM also takes every peer's stores during
+    the step (§5 of DESIGN.md): the extra units then go to the ranks farthest from it (light=0: 12,12,12,12,13,13,13,13)."""
     assert n >= 0 and world >= 1
     base, extra = divmod(n, world)
+    if light is None:
+        heavy = set(range(extra))
+    else:
+        order = sorted(range(world), key=lambda r: (-min((r - light) % world, (light - r) % world), r))
+        heavy = set(order[:extra])
     out, b = [], 0
     for r in range(world):
-        e = b + base + (1 if r < extra else 0)
+        e = b + base + (1 if r in heavy else 0)
         out.append((b, e))
         b = e
     return out

@@ -16,6 +16,11 @@ from syn3r_b200 import sharding, synth
 def test_partition_units_matches_survey_split():
     assert [e - b for b, e in sharding.partition_units(100, 8)] == [13, 13, 13, 13, 12, 12, 12, 12]
     assert sharding.partition_units(25, 2) == [(0, 13), (13, 25)]
+    # the diffusion rank (which ingests the peers' stores) gets the light share, the extras go far from it
+    lens = [e - b for b, e in sharding.partition_units(100, 8, light=0)]
+    assert sum(lens) == 100 and lens[0] == 12 and sorted(lens) == [12] * 4 + [13] * 4
+    assert [e - b for b, e in sharding.partition_units(25, 8, light=0)][0] == 3
+    assert sharding.partition_units(25, 2, light=0) == [(0, 12), (12, 25)]
     assert sharding.partition_units(3, 4) == [(0, 1), (1, 2), (2, 3), (3, 3)]
     for n in (0, 1, 7, 25, 64, 100):
         for w in (1, 2, 3, 4, 8):
