@@ -6,8 +6,9 @@ There is no CPU path: without the CUDA library (or a GPU) these functions raise.
 
 Differences a caller can observe (documented in DESIGN.md):
   * the colour-range failure of forward_warp.py:121-125 raises AssertionError instead of opening pdb;
-  * colours are accumulated in fp32: uint8 outputs can differ by one level at rounding
-    ties (about 1e-5 of values), float outputs agree to < 1e-5 on the [0,1] scale; masks are bit-exact;
+  * colours are accumulated in integer block floating point with 21-22 significant bits per cell (DESIGN.md 4.1;
+    the reference accumulates in float64): uint8 outputs can differ by one level at rounding ties
+    (about 3e-5 of values), float outputs agree to < 1e-5 on the [0,1] scale; masks are bit-exact;
   * float64 images are rounded to float32 on upload (depth, poses and intrinsics keep full precision).
 """
 from __future__ import annotations
