@@ -410,8 +410,12 @@ __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__res
 // shared-memory counter) is in flight too, so neither the L2 latency nor the claim is exposed at a work-unit
 // boundary, and the unit of the dynamic scheduler is one iteration (2 x 32 px): short tails at the barrier that ends
 // the sweep.  (The former fx_block took 4-row units and exposed one L2 round trip + one claim per unit.)
+// Measured (round 2): no gain on config B (1.285 vs 1.293 ms alone; 1.250 vs 1.248 ms next to the other changes) - the
+// L2 round trip and the claim at a work-unit boundary are not what the warps wait for - and 7 % SLOWER on config E
+// (1459 vs 1351 ms: the two-level cull hands over many short block lists, each paying the pipeline's fill and two
+// surplus claims per warp).  Off by default; kept for A/B.
 #ifndef SYN3R_FX_STREAM
-#define SYN3R_FX_STREAM 1
+#define SYN3R_FX_STREAM 0
 #endif
 template <bool WINNER, int SWEEP>
 __device__ __forceinline__ void fx_stream(const TileArgs &a, const FxAux &sm, const FxPairRegs &pr, int p, int s, int nB,
