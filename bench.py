@@ -359,8 +359,10 @@ def run_ours(args):
     H, W, hw = wl.H, wl.W, wl.H * wl.W
     big = wl.lazy_sources                                         # config E: GBs of inputs / outputs per rank
     strong = world > 1 and not args.weak
-    # strong scaling: rank 0 (the diffusion rank) also ingests every peer's stores, so it gets a light share
-    parts = sharding.partition_units(wl.frames, world, light=0) if strong else [(0, wl.frames)] * world
+    # (measured, N = 8, config B: giving rank 0 - which also ingests every peer's stores - the LIGHT share,
+    # partition_units(light=0), is slower, 0.503 vs 0.477 ms: a heavy rank's extra frame is cheapest where its stores
+    # are local, and the peers' stores then have the whole step to drain)
+    parts = sharding.partition_units(wl.frames, world) if strong else [(0, wl.frames)] * world
     f0, f1 = parts[rank]
     packed = strong and args.wire == "compact" and hw % 16 == 0     # the 0/1 masks travel as bits (np.packbits order)
     share = workload.build_plan(wl, f0, f1, seed=(0 if (strong or world == 1) else rank), want_f32=True, want_u8=strong,
