@@ -359,14 +359,24 @@ def run_ours(args):
     H, W, hw = wl.H, wl.W, wl.H * wl.W
     big = wl.lazy_sources                                         # config E: GBs of inputs / outputs per rank
     strong = world > 1 and not args.weak
-    # (measured, N = 8, config B: giving rank 0 - which also ingests every peer's stores - the LIGHT share,
-    # partition_units(light=0), is slower, 0.503 vs 0.477 ms: a heavy rank's extra frame is cheapest where its stores
-    # are local, and the peers' stores then have the whole step to drain)
-    parts = sharding.partition_units(wl.frames, world) if strong else [(0, wl.frames)] * world
+    # strong scaling: the workload's output slots (pair warps in PAIR mode, frames in FUSED mode) in contiguous blocks, one
+    # per rank; in PAIR mode the cut may fall inside a target frame (75 pair warps over 8 GPUs: 10,10,10,9,... instead of
+    # 4,3,3,... frames).  (Measured, N = 8, config B: giving rank 0 - which also ingests every peer's stores - a LIGHT
+    # share is slower, 0.503 vs 0.477 ms: a heavy rank's extra work is cheapest where its stores are local.)
+    slot_parts = workload.partition_slots(wl, world) if strong else [(0, sum(workload.slots_per_frame(wl)))] * world
+    parts, trims = [], []
+    for q0, q1 in slot_parts:
+        if q1 > q0:
+            a, b, h, t = workload.frames_of_slots(wl, q0, q1)
+        else:
+            a, b, h, t = 0, 0, 0, 0
+        parts.append((a, b))
+        trims.append((h, t))
     f0, f1 = parts[rank]
+    assert f1 > f0, "more ranks than output slots"
     packed = strong and args.wire == "compact" and hw % 16 == 0     # the 0/1 masks travel as bits (np.packbits order)
-    share = workload.build_plan(wl, f0, f1, seed=(0 if (strong or world == 1) else rank), want_f32=True, want_u8=strong,
-                                want_winner=True, pack_masks=packed)
+    share = workload.build_plan(wl, f0, f1, seed=(0 if (strong or world == 1) else rank), trim=trims[rank], want_f32=True,
+                                want_u8=strong, want_winner=True, pack_masks=packed)
     tw = share.plan
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
@@ -398,7 +408,7 @@ def run_ours(args):
     # ---- N > 1: the gather of the finished frames on the diffusion rank is part of the step ---------------------
     gather_info, step, counts = None, tw.run, None
     if strong:
-        counts = [len(workload_slots(wl, a, b)) for a, b in parts]
+        counts = [q1 - q0 for q0, q1 in slot_parts]
         if args.wire == "post":
             tw._alloc_post()
             tw.post = True
@@ -537,7 +547,7 @@ def run_ours(args):
         if world == 1:
             e2e, e2e_all, e2e_post, e2e_dropin = e2e_single(args, wl, share, timed, mpix_step, big)
         elif strong:
-            e2e = e2e_strong(args, wl, share, parts, timed, mpix_step, dev, rank, world, all_max)
+            e2e = e2e_strong(args, wl, share, parts, trims, slot_parts, timed, mpix_step, dev, rank, world, all_max)
 
     cpu, parity = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -549,7 +559,7 @@ def run_ours(args):
     if rank == 0:
         extra = {}
         if world > 1:
-            extra["partition"] = ({"frames_per_rank": [b - a for a, b in parts], "slots_per_rank": counts} if strong
+            extra["partition"] = ({"slots_per_rank": counts, "frames_touched_per_rank": [b - a for a, b in parts]} if strong
                                   else "one whole workload per rank (seed = rank), no collective")
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
@@ -566,17 +576,6 @@ def run_ours(args):
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
-
-
-def workload_slots(wl, f0, f1):
-    """output slots (pairs in PAIR mode, frames in FUSED mode) of frames [f0, f1)"""
-    if wl.mode == "fused":
-        return list(range(f0, f1))
-    out = []
-    for f in range(f0, f1):
-        k, _ = wl.frame_owner(f)
-        out += [f] * wl.trajs[k][0]
-    return out
 
 
 def e2e_single(args, wl, share, timed, mpix_step, big):
@@ -667,7 +666,7 @@ def dropin_e2e(wl, share, mpix_step, max_pairs=24):
                    "flow12 / 11-key dict the reference returns): wall clock, scaled from the timed pairs to the whole step"}
 
 
-def e2e_strong(args, wl, share, parts, timed, mpix_step, dev, rank, world, all_max):
+def e2e_strong(args, wl, share, parts, trims, slot_parts, timed, mpix_step, dev, rank, world, all_max):
     """N > 1, ONE consumer: host inputs on rank 0 -> H2D -> broadcast over NVLink -> partitioned warps -> gather of the
     reference-facing outputs on rank 0 -> D2H on rank 0 only."""
     import torch
@@ -686,10 +685,10 @@ def e2e_strong(args, wl, share, parts, timed, mpix_step, dev, rank, world, all_m
         del sh0
     f0, f1 = parts[rank]
     # its own plan with local outputs (the `value` plan may be writing into rank 0's peer buffers)
-    tw = workload.build_plan(wl, f0, f1, seed=0, want_f32=False, want_u8=True, want_winner=True,
+    tw = workload.build_plan(wl, f0, f1, seed=0, trim=trims[rank], want_f32=False, want_u8=True, want_winner=True,
                              pack_masks=(wl.H * wl.W) % 16 == 0).plan
     local_wire = sharding.compact_wire(tw.out_fwd, tw.out_inv)
-    counts = [len(workload_slots(wl, a, b)) for a, b in parts]
+    counts = [q1 - q0 for q0, q1 in slot_parts]
     pg = sharding.PipelinedGather(local_wire, counts, args.gather_chunks, dst=0)
     pinned = None
     if rank == 0:

@@ -110,9 +110,38 @@ class RankShare:
     host_tgt: torch.Tensor = None
 
 
-def build_plan(wl: Workload, f0: int, f1: int, seed: int = 0, **plan_kw) -> RankShare:
+def slots_per_frame(wl: Workload) -> List[int]:
+    """Output slots of every target frame in order: S pair warps in PAIR mode, one fused frame in FUSED mode."""
+    out = []
+    for S, T in wl.trajs:
+        out += [S if wl.mode == "pair" else 1] * T
+    return out
+
+
+def partition_slots(wl: Workload, world: int):
+    """The workload's output slots (pair warps, target-major; frames in FUSED mode) cut into `world` contiguous blocks:
+    [(q0, q1)] per rank.  In PAIR mode a (source, target) pair is the independent unit of work, so the cut
+    may fall INSIDE a target frame: 25 frames x 3 sources over 8 GPUs is 10,10,10,9,9,9,9,9 pair warps instead of
+    4,3,3,3,3,3,3,3 frames (12 pair warps on the heaviest rank).  FUSED mode: slots are frames (13,13,13,13,12,12,12,12)."""
+    from . import sharding
+    return sharding.partition_units(sum(slots_per_frame(wl)), world)
+
+
+def frames_of_slots(wl: Workload, q0: int, q1: int):
+    """(f0, f1, head, tail): the frames [f0, f1) that slots [q0, q1) touch, and how many slots of frame f0 / f1-1 lie
+    OUTSIDE the range (to be trimmed from the frames' slot list)."""
+    assert q0 < q1
+    spf = slots_per_frame(wl)
+    starts = np.concatenate([[0], np.cumsum(spf)])
+    f0 = int(np.searchsorted(starts, q0, side="right") - 1)
+    f1 = int(np.searchsorted(starts, q1, side="left"))
+    return f0, f1, int(q0 - starts[f0]), int(starts[f1] - q1)
+
+
+def build_plan(wl: Workload, f0: int, f1: int, seed: int = 0, trim=(0, 0), **plan_kw) -> RankShare:
     """Plan + synthetic inputs (uploaded, device resident; pinned host staging filled when pinned_host=True) for frames
-    [f0, f1).  Trajectory k of the workload uses seed `seed + k`."""
+    [f0, f1).  Trajectory k of the workload uses seed `seed + k`.  `trim` = (head, tail): that many pair warps of the
+    first / last frame belong to a neighbouring rank (`frames_of_slots`; PAIR mode only)."""
     assert 0 <= f0 < f1 <= wl.frames
     H, W = wl.H, wl.W
     ids, base, local_T = [], [], []
@@ -137,6 +166,11 @@ def build_plan(wl: Workload, f0: int, f1: int, seed: int = 0, **plan_kw) -> Rank
                 pair_global.append((k, s, t))
         sb += S
         tb += t1 - t0
+    head, tail = int(trim[0]), int(trim[1])
+    if head or tail:
+        assert wl.mode == "pair" and head + tail < len(ps)
+        keep = slice(head, len(ps) - tail)
+        ps, pt, pair_global = ps[keep], pt[keep], pair_global[keep]
     ps, pt = np.asarray(ps, np.int32), np.asarray(pt, np.int32)
     fr0 = [sum(T for _, T in wl.trajs[:k]) for k in ids]
     if wl.mode == "fused":

@@ -54,3 +54,23 @@ def test_fused_plan_and_slot_ranges():
                                want_f32=False, want_u8=False)
     assert torch.equal(o["mask"].bool().any(0), whole["mask"][0].bool())
     assert torch.equal(whole["winner"][0] >= 0, whole["mask"][0].bool())
+
+
+@pytest.mark.parametrize("world", [2, 3, 4])
+def test_slot_partition_inside_a_frame_reassembles_the_workload(world):
+    """PAIR mode: the ranks' shares cut at PAIR granularity (workload.partition_slots: the cut may fall inside a target
+    frame) and laid out at their slot offsets equal the one-GPU plan, bit for bit."""
+    wl = workload.Workload("mini_B", "pair", True, 48, 64, [(3, 5)])                 # 15 pair warps
+    full = workload.build_plan(wl, 0, wl.frames, seed=3, want_f32=False, want_u8=True, want_winner=False).plan
+    ref = full.run()
+    torch.cuda.synchronize()
+    parts = workload.partition_slots(wl, world)
+    assert sum(q1 - q0 for q0, q1 in parts) == 15 and max(q1 - q0 for q0, q1 in parts) - min(q1 - q0 for q0, q1 in parts) <= 1
+    for q0, q1 in parts:
+        f0, f1, head, tail = workload.frames_of_slots(wl, q0, q1)
+        sh = workload.build_plan(wl, f0, f1, seed=3, trim=(head, tail), want_f32=False, want_u8=True, want_winner=False)
+        assert sh.plan.P == q1 - q0 and len(sh.frame_of_slot) == q1 - q0
+        o = sh.plan.run()
+        torch.cuda.synchronize()
+        assert torch.equal(o.mask, ref.mask[q0:q1]) and torch.equal(o.rgb_u8, ref.rgb_u8[q0:q1])
+        assert torch.equal(o.mask_reproj, ref.mask_reproj[q0:q1]) and torch.equal(o.soft_mask_reproj, ref.soft_mask_reproj[q0:q1])

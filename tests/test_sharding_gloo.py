@@ -185,3 +185,22 @@ def test_workload_partition_cuts_trajectories_first_then_frames():
     we = workload.for_config("E_stress")
     assert we.mode == "fused" and not we.consistency and we.frames == 100
     assert [b - a for a, b in sharding.partition_units(we.frames, 8)] == [13, 13, 13, 13, 12, 12, 12, 12]
+
+
+def test_slot_partition_cuts_pairs_not_frames():
+    """PAIR mode: 75 pair warps (25 frames x 3 sources) over 8 GPUs are 10,10,10,9,9,9,9,9 pair warps - the cut may fall
+    inside a frame - where a frame partition would leave 12 on one rank; FUSED mode keeps whole frames."""
+    from syn3r_b200 import workload
+    wb = workload.for_config("B_svd")
+    parts = workload.partition_slots(wb, 8)
+    assert [q1 - q0 for q0, q1 in parts] == [10, 10, 10, 9, 9, 9, 9, 9]
+    touched = [workload.frames_of_slots(wb, q0, q1) for q0, q1 in parts]
+    assert touched[0] == (0, 4, 0, 2)            # slots 0..9 = frames 0..2 whole + 1 pair of frame 3
+    assert touched[1] == (3, 7, 1, 1)            # slots 10..19: frame 3 minus its first pair ... frame 6 minus its last
+    for (q0, q1), (f0, f1, h, t) in zip(parts, touched):
+        assert 3 * (f1 - f0) - h - t == q1 - q0
+    we = workload.for_config("E_stress")
+    assert [q1 - q0 for q0, q1 in workload.partition_slots(we, 8)] == [13, 13, 13, 13, 12, 12, 12, 12]
+    wd = workload.for_config("D_dl3dv")
+    assert [q1 - q0 for q0, q1 in workload.partition_slots(wd, 8)] == [50] * 8
+    assert [workload.frames_of_slots(wd, q0, q1) for q0, q1 in workload.partition_slots(wd, 8)][3] == (75, 100, 0, 0)
