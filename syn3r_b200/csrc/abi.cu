@@ -87,6 +87,8 @@ struct FwdWorkspace {
     int *redo_list;
     double *blk_zhi;
     unsigned long long *zlo;
+    unsigned *tile_cnt;         // per-(pair, tile) block lists (NULL: frame too large for the one-pass cull)
+    int *tile_list;
     size_t bytes, acc_bytes, keys_bytes, small_bytes;
 };
 
@@ -107,7 +109,9 @@ static FwdWorkspace fwd_layout(void *base, int H, int W, int S, int n_pairs, int
         return w;
     }
     TileGeom g = make_geom(H, W);
-    w.small_bytes = zb + nb + 256 + zb;                 // ... + zlo keys
+    const bool lists = SYN3R_FX_TILE_LISTS && g.nsb * SYN3R_SB_BLOCKS <= SYN3R_FX_FLAT;
+    const size_t cnt_b = lists ? align_up((size_t)n_pairs * g.ntiles * 4, 256) : 0;
+    w.small_bytes = zb + nb + 256 + zb + cnt_b;         // ... + zlo keys + tile-list counts (all zeroed per call)
     size_t stats_b = align_up((size_t)S * g.nsb * SYN3R_SB_BLOCKS * sizeof(BlockStats), 256);
     size_t blk_b = align_up((size_t)n_pairs * g.nsb * SYN3R_SB_BLOCKS * sizeof(CellBox), 256);
     size_t sb_b = align_up((size_t)n_pairs * g.nsb * sizeof(CellBox), 256);
@@ -124,7 +128,10 @@ static FwdWorkspace fwd_layout(void *base, int H, int W, int S, int n_pairs, int
     size_t zhi_b = align_up((size_t)n_pairs * g.nsb * SYN3R_SB_BLOCKS * sizeof(double), 256);
     w.blk_zhi = (double *)(b + w.small_bytes + stats_b + blk_b + sb_b + pf_b + redo_b);
     w.zlo = (unsigned long long *)(b + zb + nb + 256);
-    w.bytes = w.small_bytes + stats_b + blk_b + sb_b + pf_b + redo_b + zhi_b;
+    const size_t list_b = lists ? align_up((size_t)n_pairs * g.ntiles * SYN3R_TILE_LIST_CAP * 4, 256) : 0;
+    w.tile_cnt = lists ? (unsigned *)(b + zb + nb + 256 + zb) : nullptr;
+    w.tile_list = lists ? (int *)(b + w.small_bytes + stats_b + blk_b + sb_b + pf_b + redo_b + zhi_b) : nullptr;
+    w.bytes = w.small_bytes + stats_b + blk_b + sb_b + pf_b + redo_b + zhi_b + list_b;
     return w;
 }
 
@@ -146,14 +153,14 @@ static int launch_tile(const TileArgs &ta, int n_items, cudaStream_t st) {
 }
 
 // fixed-point kernel, then the fp32 kernel over whatever work items it handed back (normally none)
-template <bool WINNER, bool FLAT>
+template <bool WINNER, bool FLAT, bool AHEAD>
 static int launch_tile_fx_as(const TileArgs &ta, int n_items, cudaStream_t st) {
     static thread_local int configured_dev = -1;
     const size_t smem = fx_smem_bytes(WINNER), smem_redo = tile_smem_bytes(WINNER);
     int dev = -1;
     SYN3R_TRY_CUDA(cudaGetDevice(&dev));
     if (configured_dev != dev) {
-        SYN3R_TRY_CUDA(cudaFuncSetAttribute(k_fwd_tile_fx<WINNER, FLAT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        SYN3R_TRY_CUDA(cudaFuncSetAttribute(k_fwd_tile_fx<WINNER, FLAT, AHEAD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)smem));
         SYN3R_TRY_CUDA(cudaFuncSetAttribute(k_fwd_tile<WINNER, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)smem_redo));
@@ -161,7 +168,7 @@ static int launch_tile_fx_as(const TileArgs &ta, int n_items, cudaStream_t st) {
     }
     int grid = sm_count() * (SYN3R_FX_TWO_CTAS ? 2 : 1);
     if (grid > n_items) grid = n_items;
-    k_fwd_tile_fx<WINNER, FLAT><<<grid, SYN3R_TILE_THREADS, smem, st>>>(ta);
+    k_fwd_tile_fx<WINNER, FLAT, AHEAD><<<grid, SYN3R_TILE_THREADS, smem, st>>>(ta);
     TileArgs tr = ta;
     tr.redo_mode = 1;
     k_fwd_tile<WINNER, false><<<grid, SYN3R_TILE_THREADS, smem_redo, st>>>(tr);
@@ -170,8 +177,10 @@ static int launch_tile_fx_as(const TileArgs &ta, int n_items, cudaStream_t st) {
 // frames of up to SYN3R_FX_FLAT source blocks (1024 x 576 and smaller) take the one-pass cull
 template <bool WINNER>
 static int launch_tile_fx(const TileArgs &ta, int n_items, cudaStream_t st) {
-    return (ta.g.nsb * SYN3R_SB_BLOCKS <= SYN3R_FX_FLAT) ? launch_tile_fx_as<WINNER, true>(ta, n_items, st)
-                                                         : launch_tile_fx_as<WINNER, false>(ta, n_items, st);
+    if (ta.g.nsb * SYN3R_SB_BLOCKS > SYN3R_FX_FLAT) return launch_tile_fx_as<WINNER, false, false>(ta, n_items, st);
+    // PAIR mode with block lists: every work item is claimed and staged one item ahead
+    if (SYN3R_FX_PREFETCH && !ta.pair_slot && ta.tile_cnt) return launch_tile_fx_as<WINNER, true, true>(ta, n_items, st);
+    return launch_tile_fx_as<WINNER, true, false>(ta, n_items, st);
 }
 
 }  // namespace syn3r
@@ -284,10 +293,10 @@ int syn3r_forward_warp_batched(const float *rgbd, const double *depth64, const u
             // boxes + bounds of z' per block, then the exact max z' over the blocks that can hold it
             k_fwd_prep<<<dim3(g.nsb, P), 32, 0, st>>>((const float4 *)rgbd, depth64, Kinv_src, pair_par, pair_src, g,
                                                       ws.stats, ws.zmax, ws.znan, ws.blk_box, ws.sb_box, ws.pair_fast,
-                                                      1, ws.blk_zhi, ws.zlo);
+                                                      1, ws.blk_zhi, ws.zlo, ws.tile_cnt, ws.tile_list);
             k_fwd_prep<<<dim3(g.nsb, P), 256, 0, st>>>((const float4 *)rgbd, depth64, Kinv_src, pair_par, pair_src, g,
                                                        ws.stats, ws.zmax, ws.znan, ws.blk_box, ws.sb_box, ws.pair_fast,
-                                                       2, ws.blk_zhi, ws.zlo);
+                                                       2, ws.blk_zhi, ws.zlo, nullptr, nullptr);
             k_fwd_finalize<<<(P + 127) / 128, 128, 0, st>>>(ws.zmax, ws.znan, P, ws.pair_fast);
         }
         if (phases & SYN3R_FWD_PHASE_SPLAT) {
@@ -297,7 +306,7 @@ int syn3r_forward_warp_batched(const float *rgbd, const double *depth64, const u
             }
             if (out_status) SYN3R_TRY_CUDA(cudaMemsetAsync(out_status, 0, (size_t)n_slots * 4, st));
             TileArgs ta{(const float4 *)rgbd, depth64, src_mask, Kinv_src, pair_par, pair_src, pair_slot, P, n_slots,
-                        flags, g, ws.zmax, ws.znan, ws.blk_box, ws.sb_box, ws.counter, out_rgb_f32, out_rgb_u8,
+                        flags, g, ws.zmax, ws.znan, ws.blk_box, ws.sb_box, ws.tile_cnt, ws.tile_list, ws.counter, out_rgb_f32, out_rgb_u8,
                         out_mask, out_winner, out_status, ws.pair_fast, ws.counter + 16, ws.redo_list,
                         ws.counter + 32, ws.counter + 48, 0};
             const int n_items = n_slots * g.ntiles;
@@ -384,4 +393,12 @@ int syn3r_bilinear_splat(const float *frame, const uint8_t *mask1, const double 
     return check_cuda(cudaGetLastError(), "bilinear_splat launches");
 }
 
+#if SYN3R_FX_PHASE_CLOCKS
+// A/B build only (tools/phase_clocks.py): per-CTA phase cycle sums of the last k_fwd_tile_fx launch
+int syn3r_debug_fx_phase(unsigned long long *host_out, int n_ctas) {
+    SYN3R_TRY_CUDA(cudaDeviceSynchronize());
+    SYN3R_TRY_CUDA(cudaMemcpyFromSymbol(host_out, g_fx_phase, sizeof(unsigned long long) * 8 * (size_t)n_ctas));
+    return SYN3R_OK;
+}
+#endif
 }  // extern "C"

@@ -38,6 +38,39 @@ namespace syn3r {
 #define SYN3R_FX_UNIT_ROWS 4            /* rows of a source block one warp takes at a time (2 per iteration) */
 #endif
 #define SYN3R_FX_UNITS (SYN3R_BLK_H / SYN3R_FX_UNIT_ROWS)
+// End game of a sweep: the last SYN3R_FX_TAIL_UNITS work units of a block list are handed out as single iterations
+// (2 rows) instead of 4-row units, so that the warps reach the barrier that ends the sweep within one iteration of each
+// other (measured with SYN3R_FX_PHASE_CLOCKS: the tails were 4 % + 10 % of the kernel with 4-row units throughout).
+#ifndef SYN3R_FX_TAIL_UNITS
+#define SYN3R_FX_TAIL_UNITS 0
+#endif
+// SYN3R_FX_PREFETCH: PAIR mode with block lists - the NEXT work item is claimed while sweep 2 of the current one runs,
+// and its per-pair constants, its source index and its block list are copied global -> shared by cp.async during the
+// resolve step (no registers held, listB is free by then), so that an item no longer starts with three dependent L2
+// round trips (work counter -> pair constants -> list) in front of its first barrier.
+#ifndef SYN3R_FX_PREFETCH
+#define SYN3R_FX_PREFETCH 1
+#endif
+__device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_4(void *smem_dst, const void *gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+// The resolve step is a burst of shared-memory loads, then arithmetic, then stores, and all 24 warps walk through those
+// phases together (LSU idle while they compute, issue slots idle while they load).  SYN3R_FX_RESOLVE_STAGGER_NS > 0:
+// half of the warps of every scheduler start that many nanoseconds later, so that one half's loads and stores overlap
+// the other half's arithmetic.
+#ifndef SYN3R_FX_RESOLVE_STAGGER_NS
+#define SYN3R_FX_RESOLVE_STAGGER_NS 0
+#endif
+// rows of a source block a thread takes per iteration (independent dependency chains per thread).  2 = the default
+// (768 threads at 80 registers); 3 / 4 = A/B builds for fewer, wider threads (SYN3R_TILE_THREADS=512 at 128 registers)
+#ifndef SYN3R_FX_ROWS
+#define SYN3R_FX_ROWS 2
+#endif
 #define SYN3R_FX_FLAT 2304    /* FLAT kernels: frames of up to this many source blocks (a 1024 x 576 frame), culled in one
                                  pass; listB holds them all */
 #if SYN3R_FX_TWO_CTAS
@@ -60,6 +93,18 @@ namespace syn3r {
 #ifndef SYN3R_FX_TRASH_SPLIT
 #define SYN3R_FX_TRASH_SPLIT 1
 #endif
+// SYN3R_FX_PHASE_CLOCKS (A/B build, tools/phase_clocks.py): per-CTA cycle sums of the phases of a work item
+//   [0] claim  [1] cull  [2] sweep 1 until its first warp runs dry  [3] sweep-1 tail (until the barrier releases)
+//   [4] sweep 2 until its first warp runs dry  [5] sweep-2 tail  [6] resolve  [7] items
+#ifndef SYN3R_FX_PHASE_CLOCKS
+#define SYN3R_FX_PHASE_CLOCKS 0
+#endif
+#if SYN3R_FX_PHASE_CLOCKS
+__device__ unsigned long long g_fx_phase[1024 * 8];
+#define FX_CLK(slot) do { if (threadIdx.x == 0) sm.ctl[slot] = (int)clock(); } while (0)
+#else
+#define FX_CLK(slot) do { } while (0)
+#endif
 #define SYN3R_FX_MAGIC 12582912.0f          /* 1.5 * 2^23: low mantissa bits of (v + MAGIC) are rint(v) */
 #define SYN3R_FX_MAGIC_BITS 0x4B400000
 
@@ -76,7 +121,9 @@ enum { FX_WMAX = 0, FX_S = 1, FX_I0 = 2, FX_I1 = 3, FX_I2 = 4, FX_N = 5, FX_ZKEY
 struct FxAux {                  // the rest of the shared memory, behind the planes
     double2 *logtab;
     int *listA, *listB, *ctl;
+    unsigned char *stage;       // staged constants of the next work item: PairFast (128 B), list count, source index
 };
+static_assert(sizeof(PairFast) == 128, "the staging area and its 8 x 16-byte copies assume a 128-byte PairFast");
 
 struct PixelGeom {              // where a source pixel lands relative to the tile
     int lxf, lyf;               // local cell of the floor corner
@@ -353,10 +400,114 @@ __device__ __forceinline__ void fx_rows2(const TileArgs &a, const double2 *__res
     }
 }
 
+
+#if SYN3R_FX_ROWS != 2
+// fx_rows2 / fx_block for R = SYN3R_FX_ROWS rows per thread and iteration (same stages, same arithmetic, arrays of R).
+template <bool WINNER, int SWEEP, int R>
+__device__ __forceinline__ void fx_rowsN(const TileArgs &a, const double2 *__restrict__ logtab, const FxPairRegs &pr,
+                                         const RowProj (&rp)[R], const float4 (&px)[R], const bool (&cand)[R], int p,
+                                         int s, int x, int y, const unsigned (&i)[R], int tx0, int ty0, int tw, int th,
+                                         float cs_inv, int lane) {
+    bool c_any = false;
+#pragma unroll
+    for (int j = 0; j < R; ++j) c_any = c_any || cand[j];
+    if (!__any_sync(0xffffffffu, c_any)) return;
+    PixelGeom g[R];
+    bool any[R], full[R];
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+        const float zf = fabsf(__double2float_rn(rp[j].q2)), df = fabsf(px[j].w);
+        const float lhs = __fmul_rn(fminf(fabsf(rp[j].fx), fabsf(rp[j].fy)), zf);
+        const float rhs = __fmaf_rn(zf, pr.k2, __fmaf_rn(df, pr.k1, pr.k0));
+        bool slow = !(lhs > rhs);
+        if (WINNER)
+            slow = slow || ((unsigned)__double2loint(rp[j].q2) + 16384u < 32768u) ||
+                   !(__fmul_rn(zf, 1.8e-12f) > __fmaf_rn(df, pr.k3, pr.k4));
+        const bool negx = rp[j].fx < 0.0f, negy = rp[j].fy < 0.0f;
+        g[j].lxf = rp[j].nx1 - (negx ? 2 : 1); g[j].lyf = rp[j].ny1 - (negy ? 2 : 1);
+        g[j].ax = negx ? -rp[j].fx : __fsub_rn(1.0f, rp[j].fx); g[j].bx = negx ? __fadd_rn(1.0f, rp[j].fx) : rp[j].fx;
+        g[j].ay = negy ? -rp[j].fy : __fsub_rn(1.0f, rp[j].fy); g[j].by = negy ? __fadd_rn(1.0f, rp[j].fy) : rp[j].fy;
+        g[j].z = rp[j].q2;
+        const bool exact = cand[j] && slow;
+        if (exact)
+            g[j] = exact_pixel(a.pair_par + (size_t)p * 24, a.Kinv_src + (size_t)s * 9, x, y + j, (double)px[j].w, tx0,
+                               ty0, tw, th);
+        any[j] = cand[j] && (unsigned)(g[j].lxf + 1) <= (unsigned)tw && (unsigned)(g[j].lyf + 1) <= (unsigned)th;
+        full[j] = cand[j] && !exact && (unsigned)g[j].lxf < (unsigned)(tw - 1) && (unsigned)g[j].lyf < (unsigned)(th - 1);
+    }
+    bool a_any = false, lean = true;
+#pragma unroll
+    for (int j = 0; j < R; ++j) { a_any = a_any || any[j]; lean = lean && (full[j] || !any[j]); }
+    if (!__any_sync(0xffffffffu, a_any)) return;
+    float wsc[R];
+    if (SWEEP == 1 && pr.upper_ok) {
+#pragma unroll
+        for (int j = 0; j < R; ++j) wsc[j] = fx_weight_upper(pr.cexp_f, __double2float_rn(g[j].z));
+    } else {
+#pragma unroll
+        for (int j = 0; j < R; ++j) wsc[j] = fx_weight_scale(logtab, pr.cexp, any[j] ? g[j].z : 1.0, pr.clamp_hi);
+    }
+    if (__all_sync(0xffffffffu, lean)) {
+#pragma unroll
+        for (int j = 0; j < R; ++j)
+            if (any[j]) fx_corners<WINNER, SWEEP, true>(g[j], wsc[j], px[j], i[j], cs_inv, lane, tw, th);
+    } else {
+#pragma unroll
+        for (int j = 0; j < R; ++j)
+            if (any[j]) fx_corners<WINNER, SWEEP, false>(g[j], wsc[j], px[j], i[j], cs_inv, lane, tw, th);
+    }
+}
+
+template <bool WINNER, int SWEEP>
+__device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__restrict__ logtab, const FxPairRegs &pr,
+                                         int p, int s, int bx0, int by0, int nrows, int tx0, int ty0, int tw, int th, int lane,
+                                         float cs_inv) {
+    constexpr int R = SYN3R_FX_ROWS;
+    const int W = a.g.W, H = a.g.H;
+    const int x = bx0 + lane;
+    const bool live = x < W;
+    const unsigned i0 = (unsigned)s * (unsigned)(H * W) + (unsigned)by0 * W + (live ? x : 0);
+    const double xd = (double)x;
+    const double u0 = __fma_rn(pr.A[0], xd, pr.A[2]), u1 = __fma_rn(pr.A[3], xd, pr.A[5]),
+                 u2 = __fma_rn(pr.A[6], xd, pr.A[8]);
+    const double tx1d = (double)(tx0 - 1), ty1d = (double)(ty0 - 1);
+    const int rows = min(nrows, H - by0);                      // this unit's rows inside the image
+    if (rows <= 0) return;
+    const float4 *src = a.rgbd + i0;
+    const uint64_t keep = l2_policy_evict_last();
+    float4 nxt[R];                                              // a row index past the unit re-reads its last row
+#pragma unroll
+    for (int j = 0; j < R; ++j) nxt[j] = ld_keep_f4(src + (unsigned)(min(j, rows - 1) * W), keep);
+    unsigned ia = i0;
+#pragma unroll 1
+    for (int r = 0; r < rows; r += R, ia += (unsigned)(R * W)) {
+        float4 px[R];
+#pragma unroll
+        for (int j = 0; j < R; ++j) px[j] = nxt[j];
+        if (r + R < rows) {
+#pragma unroll
+            for (int j = 0; j < R; ++j) nxt[j] = ld_keep_f4(src + (unsigned)(min(r + R + j, rows - 1) * W), keep);
+        }
+        const int y = by0 + r;
+        const double yd = (double)y;
+        RowProj rp[R];
+        bool cand[R];
+        unsigned i[R];
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            rp[j] = fx_project(pr, u0, u1, u2, __dadd_rn(yd, (double)j), (double)px[j].w, tx1d, ty1d, tw, th);
+            cand[j] = rp[j].cand && live && (r + j < rows);
+            i[j] = ia + (unsigned)(j * W);
+        }
+        fx_rowsN<WINNER, SWEEP, R>(a, logtab, pr, rp, px, cand, p, s, x, y, i, tx0, ty0, tw, th, cs_inv, lane);
+        __syncwarp();
+    }
+}
+#else
 // Half a source block (32 x 4 px from row by0) of one pair, two rows per iteration.
 template <bool WINNER, int SWEEP>
 __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__restrict__ logtab, const FxPairRegs &pr,
-                                         int p, int s, int bx0, int by0, int tx0, int ty0, int tw, int th, int lane,
+                                         int p, int s, int bx0, int by0, int nrows, int tx0, int ty0, int tw, int th, int lane,
                                          float cs_inv) {
     const int W = a.g.W, H = a.g.H;
     const int x = bx0 + lane;
@@ -366,7 +517,7 @@ __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__res
     const double u0 = __fma_rn(pr.A[0], xd, pr.A[2]), u1 = __fma_rn(pr.A[3], xd, pr.A[5]),
                  u2 = __fma_rn(pr.A[6], xd, pr.A[8]);
     const double tx1d = (double)(tx0 - 1), ty1d = (double)(ty0 - 1);
-    const int rows = min(SYN3R_FX_UNIT_ROWS, H - by0);          // this unit's rows inside the image
+    const int rows = min(nrows, H - by0);                      // this unit's rows inside the image
     if (rows <= 0) return;
     const float4 *src = a.rgbd + i0;
     const unsigned W2 = 2u * (unsigned)W;
@@ -404,6 +555,8 @@ __device__ __forceinline__ void fx_block(const TileArgs &a, const double2 *__res
         __syncwarp();
     }
 }
+
+#endif  // SYN3R_FX_ROWS
 
 // One sweep over the culled block list (sm.listB, nB blocks) as a software-pipelined STREAM of row pairs: while the
 // warp works on row pair n, the two float4 rows of pair n+1 are in flight from L2 and the claim of pair n+2 (a
@@ -478,14 +631,18 @@ __device__ __forceinline__ void fx_stream(const TileArgs &a, const FxAux &sm, co
 __host__ __device__ inline size_t fx_smem_bytes(bool winner) {
     const size_t cells = (size_t)SYN3R_TILE_W * SYN3R_TILE_H;
     return (cells + SYN3R_TILE_W) * 4 * (winner ? 8 : 6) + (SYN3R_FX_TWO_CTAS ? 0 : (size_t)SYN3R_LOGTAB * 16) +
-           (SYN3R_LISTA + SYN3R_FX_LISTB_CAP) * 4 + 64;
+           (SYN3R_LISTA + SYN3R_FX_LISTB_CAP) * 4 + 64 + 192;
 }
 
 // culls the pair's source blocks against the tile and runs one sweep over the survivors.
-// ctl: [1] nA, [2] nB, [4] / [5] dynamic block counters of sweep 1 / 2, [6] listB is complete and reusable
+// ctl: [1] nA, [2] nB, [4] / [5] dynamic block counters of sweep 1 / 2, [14] / [15] the same for the end game (single
+// iterations), [6] listB is complete and reusable, [9..13] phase clocks (SYN3R_FX_PHASE_CLOCKS builds)
 template <bool WINNER, int SWEEP, bool FLAT>
-__device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, const FxPairRegs &pr, int p, int s,
-                                        int tx0, int ty0, int tx1, int ty1, bool reuse_list, bool fresh, float cs_inv) {
+__device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, const FxPairRegs &pr, int p, int s, int tile,
+                                        int tx0, int ty0, int tx1, int ty1, bool reuse_list, bool fresh, float cs_inv,
+                                        int staged_n = -2) {
+    // staged_n (AHEAD kernels): >= 0 = listB already holds that many blocks (copied while the previous item resolved):
+    // no cull, no barrier, in either sweep; -1 = the staged list overflowed its cap: in-kernel cull; -2 = nothing staged
     const TileGeom &g = a.g;
     const int tid = threadIdx.x, lane = tid & 31;
     const int tw = tx1 - tx0 + 1, th = ty1 - ty0 + 1;
@@ -494,17 +651,39 @@ __device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, cons
 #if SYN3R_FX_STREAM && SYN3R_FX_EXPERIMENT == 0
         fx_stream<WINNER, SWEEP>(a, sm, pr, p, s, nB, tx0, ty0, tw, th, lane, cs_inv);
 #else
+        const int units = SYN3R_FX_UNITS * nB;                  // work unit = part of a block: shorter tails
+        constexpr int SUB = SYN3R_FX_UNIT_ROWS / SYN3R_FX_ROWS; // iterations of a unit
+        const int tail_units = min(units, SYN3R_FX_TAIL_UNITS), main_units = units - tail_units;
+        bool tail = (SYN3R_FX_TAIL_UNITS != 0) && main_units == 0;
         for (;;) {
             int k = 0;
-            if (lane == 0) k = atomicAdd(&ctl[SWEEP == 1 ? 4 : 5], 1);
+            if (lane == 0) k = atomicAdd(&ctl[(SWEEP == 1 ? 4 : 5) + (tail ? 10 : 0)], 1);
             k = __shfl_sync(0xffffffffu, k, 0);
-            if (k >= SYN3R_FX_UNITS * nB) break;                // work unit = part of a block: shorter tails
-            const int org = sm.listB[k / SYN3R_FX_UNITS];       // (by0 << 16) | bx0
-            fx_block<WINNER, SWEEP>(a, sm.logtab, pr, p, s, org & 0xffff, (org >> 16) + (k % SYN3R_FX_UNITS) * SYN3R_FX_UNIT_ROWS, tx0, ty0,
-                                    tw, th, lane, cs_inv);
+            int u = k, r0 = 0, nr = SYN3R_FX_UNIT_ROWS;
+            if (!tail) {
+                if (k >= main_units) {
+                    if (SYN3R_FX_TAIL_UNITS == 0) break;
+                    tail = true;                                // this warp's first end-game claim comes next
+                    continue;
+                }
+            } else {
+                if (k >= tail_units * SUB) break;
+                u = main_units + k / SUB; r0 = (k % SUB) * SYN3R_FX_ROWS; nr = SYN3R_FX_ROWS;
+            }
+            const int org = sm.listB[u / SYN3R_FX_UNITS];       // (by0 << 16) | bx0
+            fx_block<WINNER, SWEEP>(a, sm.logtab, pr, p, s, org & 0xffff, (org >> 16) + (u % SYN3R_FX_UNITS) * SYN3R_FX_UNIT_ROWS + r0,
+                                    nr, tx0, ty0, tw, th, lane, cs_inv);
         }
+#if SYN3R_FX_PHASE_CLOCKS
+        if (lane == 0) atomicMin(reinterpret_cast<unsigned *>(&ctl[SWEEP == 1 ? 12 : 13]), (unsigned)clock() - (unsigned)ctl[9]);
+#endif
 #endif
     };
+    if (staged_n >= 0) {
+        if (SWEEP == 1) FX_CLK(10);
+        run_list(staged_n);
+        return;
+    }
     if (SWEEP == 2 && reuse_list) {       // the list sweep 1 built is complete: no culling, no barrier
         run_list(ctl[2]);
         return;
@@ -515,27 +694,43 @@ __device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, cons
         // L2 round trip and one barrier instead of the two-level cull's two and six
         if (!fresh) {                      // counters left by an earlier pair of this item
             __syncthreads();
-            if (tid == 0) { ctl[2] = 0; ctl[4] = 0; ctl[5] = 0; }
+            if (tid == 0) { ctl[2] = 0; ctl[4] = 0; ctl[5] = 0; ctl[14] = 0; ctl[15] = 0; }
             __syncthreads();
         }
-        const int nblk = g.nsb * SYN3R_SB_BLOCKS;
-        CellBox bx[SYN3R_FX_FLAT_PER_THREAD];
-#pragma unroll
-        for (int k = 0; k < SYN3R_FX_FLAT_PER_THREAD; ++k) {
-            const int j = tid + k * SYN3R_TILE_THREADS;
-            bx[k] = (j < nblk) ? bbb[j] : CellBox{1, 1, 0, 0};
+        bool listed = false;
+        if (a.tile_cnt && staged_n == -2) {
+            // the list k_fwd_prep built for this (pair, tile): one L2 round trip, no box tests
+            const size_t t = (size_t)p * g.ntiles + tile;
+            const unsigned cnt = a.tile_cnt[t];
+            int e = 0;
+            if (tid < SYN3R_TILE_LIST_CAP) e = a.tile_list[t * SYN3R_TILE_LIST_CAP + tid];
+            listed = cnt <= SYN3R_TILE_LIST_CAP;
+            if (listed) {
+                if (tid < (int)cnt) sm.listB[tid] = e;
+                if (tid == 0) ctl[2] = (int)cnt;
+            }
         }
+        if (!listed) {
+            const int nblk = g.nsb * SYN3R_SB_BLOCKS;
+            CellBox bx[SYN3R_FX_FLAT_PER_THREAD];
 #pragma unroll
-        for (int k = 0; k < SYN3R_FX_FLAT_PER_THREAD; ++k) {
-            const int j = tid + k * SYN3R_TILE_THREADS;
-            if (box_hits(bx[k], tx0, ty0, tx1, ty1)) {
-                int bx0, by0;
-                block_origin(g, j / SYN3R_SB_BLOCKS, j % SYN3R_SB_BLOCKS, bx0, by0);
-                sm.listB[atomicAdd(&ctl[2], 1)] = (by0 << 16) | bx0;
+            for (int k = 0; k < SYN3R_FX_FLAT_PER_THREAD; ++k) {
+                const int j = tid + k * SYN3R_TILE_THREADS;
+                bx[k] = (j < nblk) ? bbb[j] : CellBox{1, 1, 0, 0};
+            }
+#pragma unroll
+            for (int k = 0; k < SYN3R_FX_FLAT_PER_THREAD; ++k) {
+                const int j = tid + k * SYN3R_TILE_THREADS;
+                if (box_hits(bx[k], tx0, ty0, tx1, ty1)) {
+                    int bx0, by0;
+                    block_origin(g, j / SYN3R_SB_BLOCKS, j % SYN3R_SB_BLOCKS, bx0, by0);
+                    sm.listB[atomicAdd(&ctl[2], 1)] = (by0 << 16) | bx0;
+                }
             }
         }
         if (tid == 0 && SWEEP == 1) ctl[6] = 1;                 // read behind the barrier that ends the sweep
         __syncthreads();
+        if (SWEEP == 1) FX_CLK(10);
         run_list(ctl[2]);
         return;
     }
@@ -550,7 +745,7 @@ __device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, cons
         const int nA = ctl[1];
         for (int a0 = 0; a0 < nA; a0 += SYN3R_LISTB / SYN3R_SB_BLOCKS) {
             __syncthreads();
-            if (tid == 0) { ctl[2] = 0; ctl[4] = 0; ctl[5] = 0; }
+            if (tid == 0) { ctl[2] = 0; ctl[4] = 0; ctl[5] = 0; ctl[14] = 0; ctl[15] = 0; }
             __syncthreads();
             const int cnt = min(SYN3R_LISTB / SYN3R_SB_BLOCKS, nA - a0) * SYN3R_SB_BLOCKS;
             for (int j = tid; j < cnt; j += SYN3R_TILE_THREADS) {
@@ -568,23 +763,35 @@ __device__ __forceinline__ void fx_pair(const TileArgs &a, const FxAux &sm, cons
     }
 }
 
-struct CellOut { float v0, v1, v2; bool m, bad; int win; };
+struct CellOut { float v0, v1, v2; bool m; unsigned range; int win; };
 
-// :109-128 for one cell from its integer accumulators
+// :109-128 for one cell from its integer accumulators.  `range` = the largest bit pattern of the three colours: a
+// value is outside [0, 256] (:121-125; negative, NaN and inf included) exactly when its bit pattern, read as an
+// unsigned integer, exceeds that of 256.0f (a resolved colour is never -0.0: it is an int -> float conversion times a
+// positive factor), so the range test of a whole row is one maximum per cell and one compare per thread.
+// GATE = false (no SYN3R_FWD_GATE_0P6): a cell without contributions has S == I == 0 and an untouched winner
+// (~0u == -1), so max(S, 1) gives the zeros and the -1 of :116 without a select.
+template <bool GATE>
 __device__ __forceinline__ CellOut fx_resolve_cell(unsigned wm, unsigned S, int I0, int I1, int I2, unsigned widx,
-                                                   int flags, float cscale, float gate) {
+                                                   float cscale, float gate) {
     CellOut o;
     o.m = wm != 0u;                                            // some corner with w > 0 landed here (:112)
-    const float Sf = __uint2float_rn(S);
-    if (flags & SYN3R_FWD_GATE_0P6)                            // sum of weights <= 0.6: undo the per-cell scale
+    if (GATE) {
+        const float Sf = __uint2float_rn(S);                   // sum of weights <= 0.6: undo the per-cell scale
         o.m = o.m && (__fmul_rn(Sf, __uint_as_float((wm & 0x7f800000u) - ((unsigned)SYN3R_FX_BITS << 23))) <= gate);
-    const float inv = __fdividef(cscale, Sf);
-    o.v0 = o.m ? __fmul_rn(__int2float_rn(I0), inv) : 0.0f;   // :116
-    o.v1 = o.m ? __fmul_rn(__int2float_rn(I1), inv) : 0.0f;
-    o.v2 = o.m ? __fmul_rn(__int2float_rn(I2), inv) : 0.0f;
-    o.bad = (flags & SYN3R_FWD_IS_IMAGE) && (!(o.v0 >= 0.0f) || !(o.v0 <= 256.0f) || !(o.v1 >= 0.0f) ||
-                                             !(o.v1 <= 256.0f) || !(o.v2 >= 0.0f) || !(o.v2 <= 256.0f));   // :121-125
-    o.win = o.m ? (int)widx : -1;
+        const float inv = __fdividef(cscale, Sf);
+        o.v0 = o.m ? __fmul_rn(__int2float_rn(I0), inv) : 0.0f;   // :116
+        o.v1 = o.m ? __fmul_rn(__int2float_rn(I1), inv) : 0.0f;
+        o.v2 = o.m ? __fmul_rn(__int2float_rn(I2), inv) : 0.0f;
+        o.win = o.m ? (int)widx : -1;
+    } else {
+        const float inv = __fdividef(cscale, __uint2float_rn(max(S, 1u)));
+        o.v0 = __fmul_rn(__int2float_rn(I0), inv);
+        o.v1 = __fmul_rn(__int2float_rn(I1), inv);
+        o.v2 = __fmul_rn(__int2float_rn(I2), inv);
+        o.win = (int)widx;
+    }
+    o.range = max(max(__float_as_uint(o.v0), __float_as_uint(o.v1)), __float_as_uint(o.v2));
     return o;
 }
 __device__ __forceinline__ unsigned u8_round(float v) {      // clip + round-half-even (:127-128)
@@ -594,7 +801,9 @@ __device__ __forceinline__ unsigned u8_round(float v) {      // clip + round-hal
 #if SYN3R_FX_TWO_CTAS
 __device__ double2 g_fx_logtab[SYN3R_LOGTAB];
 #endif
-template <bool WINNER, bool FLAT>
+// AHEAD (launcher: PAIR mode, FLAT, block lists present, SYN3R_FX_PREFETCH): every work item starts with its constants
+// and its block list already in shared memory.
+template <bool WINNER, bool FLAT, bool AHEAD>
 __global__ void __launch_bounds__(SYN3R_TILE_THREADS, SYN3R_FX_TWO_CTAS ? 2 : 1)
 k_fwd_tile_fx(const TileArgs a) {
     const int CELLS = FX_PLANE, NPL = WINNER ? 8 : 6;          // plane stride incl. the trash row
@@ -607,7 +816,8 @@ k_fwd_tile_fx(const TileArgs a) {
 #endif
     sm.listA = reinterpret_cast<int *>(ptr); ptr += SYN3R_LISTA * 4;
     sm.listB = reinterpret_cast<int *>(ptr); ptr += SYN3R_FX_LISTB_CAP * 4;
-    sm.ctl = reinterpret_cast<int *>(ptr);
+    sm.ctl = reinterpret_cast<int *>(ptr); ptr += 64;
+    sm.stage = ptr;
     int *ctl = sm.ctl;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = SYN3R_TILE_THREADS / 32;
@@ -633,19 +843,57 @@ k_fwd_tile_fx(const TileArgs a) {
     const float cs_inv = cb ? __uint_as_float((254u - ce) << 23) : 1.0f;
     const int n_items = a.n_slots * g.ntiles;
     const float gate = 0.6f * (float)SYN3R_W_SCALE;
+    const bool gated = (a.flags & SYN3R_FWD_GATE_0P6) != 0;
     const uint64_t once = l2_policy_evict_first();
 
+#if SYN3R_FX_PHASE_CLOCKS
+    __shared__ unsigned long long ph[8];
+    if (tid < 8) ph[tid] = 0;
+    unsigned ph_tb = 0;
+#endif
+    // AHEAD: claim a work item and start the copies of its per-pair constants, source index and block list into shared
+    // memory (cp.async: no registers held; listB is free whenever this is called)
+    auto stage_item = [&](int it) {
+        if (it >= n_items) return;
+        const int np = it / g.ntiles;                          // PAIR mode: pair = slot
+        const size_t nt = (size_t)np * g.ntiles + (size_t)(it - np * g.ntiles);
+        if (tid < 8) cp_async_16(sm.stage + tid * 16, reinterpret_cast<const unsigned char *>(a.pair_fast + np) + tid * 16);
+        else if (tid == 8) cp_async_4(sm.stage + 128, a.tile_cnt + nt);
+        else if (tid == 9) cp_async_4(sm.stage + 132, a.pair_src + np);
+        else if (tid >= 32 && tid < 32 + SYN3R_TILE_LIST_CAP / 4)
+            cp_async_16(sm.listB + (tid - 32) * 4, a.tile_list + nt * SYN3R_TILE_LIST_CAP + (size_t)(tid - 32) * 4);
+        cp_async_commit();
+    };
+    if (AHEAD) {
+        if (tid == 0) ctl[8] = (int)atomicAdd(a.work_counter, 1u);
+        __syncthreads();
+        stage_item(ctl[8]);
+    }
     for (;;) {
         __syncthreads();
         if (tid == 0) {
-            ctl[0] = (int)atomicAdd(a.work_counter, 1u);
+#if SYN3R_FX_PHASE_CLOCKS
+            const unsigned ph_ta = (unsigned)clock();
+#endif
+            if (!AHEAD) ctl[0] = (int)atomicAdd(a.work_counter, 1u);
             ctl[2] = 0; ctl[3] = 0; ctl[4] = 0; ctl[5] = 0; ctl[6] = 0; ctl[7] = 0;   // empty block list until culled
+            ctl[14] = 0; ctl[15] = 0;
+#if SYN3R_FX_PHASE_CLOCKS
+            if (AHEAD || ctl[0] >= 0) ph_tb = (unsigned)clock();      // (depends on the atomic's result)
+            ph[0] += ph_tb - ph_ta;
+            ctl[9] = (int)ph_tb; ctl[10] = (int)ph_tb; ctl[12] = -1; ctl[13] = -1;
+#endif
         }
+        if (AHEAD) cp_async_wait_all();                        // this thread's share of the staged copies
         __syncthreads();
-        const int item = ctl[0];
+        const int item = ctl[AHEAD ? 8 : 0];                   // (AHEAD: thread 0 replaces ctl[8] behind the next barrier)
         if (item >= n_items) break;
         if (colour_bad) {
             if (tid == 0) a.redo_list[atomicAdd(a.redo_count, 1u)] = item;
+            if (AHEAD) {                                       // (nothing of the next item needs staging on this path)
+                __syncthreads();
+                if (tid == 0) ctl[8] = (int)atomicAdd(a.work_counter, 1u);
+            }
             continue;
         }
         const int slot = item / g.ntiles, tile = item - slot * g.ntiles;
@@ -653,7 +901,7 @@ k_fwd_tile_fx(const TileArgs a) {
         const int tx1 = min(tx0 + SYN3R_TILE_W, W) - 1, ty1 = min(ty0 + SYN3R_TILE_H, H) - 1;
         bool poisoned = false;
         auto load_pair = [&](int p, FxPairRegs &pr) -> bool {
-            const PairFast *pf = a.pair_fast + p;
+            const PairFast *pf = AHEAD ? reinterpret_cast<const PairFast *>(sm.stage) : a.pair_fast + p;
             pr.cexp = pf->cexp;
             if (!(pr.cexp < CUDART_INF)) return false;         // max log-depth NaN or 0: every weight is NaN (:84)
 #pragma unroll
@@ -676,15 +924,25 @@ k_fwd_tile_fx(const TileArgs a) {
             }
             if (crowded) ctl[3] = 1;
         };
-        if (!a.pair_slot) {                                    // PAIR mode: the slot's one pair, list built once
+        if (AHEAD || !a.pair_slot) {                           // PAIR mode: the slot's one pair, list built once
             FxPairRegs pr;
-            const int p = slot, s = a.pair_src[p];
+            const int p = slot, s = AHEAD ? *reinterpret_cast<const int *>(sm.stage + 132) : a.pair_src[p];
+            int staged_n = -2;
+            if (AHEAD) {
+                const unsigned cnt = *reinterpret_cast<const unsigned *>(sm.stage + 128);
+                staged_n = cnt <= SYN3R_TILE_LIST_CAP ? (int)cnt : -1;
+            }
             if (load_pair(p, pr)) {                            // (a dead pair leaves the tile empty: mask all false)
-                fx_pair<WINNER, 1, FLAT>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, true, cs_inv);
+                fx_pair<WINNER, 1, FLAT>(a, sm, pr, p, s, tile, tx0, ty0, tx1, ty1, false, true, cs_inv, staged_n);
                 __syncthreads();
+                FX_CLK(11);
+                if (AHEAD && tid == 0) ctl[8] = (int)atomicAdd(a.work_counter, 1u);    // the next item, read after sweep 2
                 scan_crowded();
                 if (SYN3R_FX_EXPERIMENT != 1 && SYN3R_FX_EXPERIMENT != 5)
-                    fx_pair<WINNER, 2, FLAT>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, FLAT || ctl[6] != 0, false, cs_inv);
+                    fx_pair<WINNER, 2, FLAT>(a, sm, pr, p, s, tile, tx0, ty0, tx1, ty1, FLAT || ctl[6] != 0, false, cs_inv, staged_n);
+            } else if (AHEAD) {
+                __syncthreads();                               // (every thread has read this item's ctl[8])
+                if (tid == 0) ctl[8] = (int)atomicAdd(a.work_counter, 1u);
             }
             __syncthreads();
         } else {                                               // FUSED mode: every pair of the slot, per sweep
@@ -697,19 +955,24 @@ k_fwd_tile_fx(const TileArgs a) {
                     FxPairRegs pr;
                     const int s = a.pair_src[p];
                     if (!load_pair(p, pr)) { poisoned = true; continue; }   // NaN weights poison cells: fp32 path
-                    if (sweep == 1) fx_pair<WINNER, 1, FLAT>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, false, cs_inv);
-                    else fx_pair<WINNER, 2, FLAT>(a, sm, pr, p, s, tx0, ty0, tx1, ty1, false, false, cs_inv);
+                    if (sweep == 1) fx_pair<WINNER, 1, FLAT>(a, sm, pr, p, s, tile, tx0, ty0, tx1, ty1, false, false, cs_inv);
+                    else fx_pair<WINNER, 2, FLAT>(a, sm, pr, p, s, tile, tx0, ty0, tx1, ty1, false, false, cs_inv);
                 }
                 __syncthreads();
             }
         }
         if (poisoned) ctl[3] = 1;
         __syncthreads();
+#if SYN3R_FX_PHASE_CLOCKS
+        const unsigned ph_t3 = (unsigned)clock();
+#endif
         const bool redo = ctl[3] != 0;                         // poisoned or crowded: k_fwd_tile recomputes the item
         if (redo && tid == 0) a.redo_list[atomicAdd(a.redo_count, 1u)] = item;
+        if (AHEAD) stage_item(ctl[8]);     // the next item's constants and block list travel while this one resolves
+                                           // (listB is free from here on)
 
         // ---- resolve from shared memory (:109-128) and clear the planes for the next item -----------------
-        bool bad = false;
+        unsigned range = 0u;                                    // largest colour bit pattern this thread resolved
         const int tw = tx1 - tx0 + 1, th = ty1 - ty0 + 1;
         const bool vec = (tw == SYN3R_TILE_W) && ((W & 3) == 0);
         const bool u8_wide = vec && ((W & 15) == 0) && ((hw & 15u) == 0u) && ((reinterpret_cast<uintptr_t>(a.out_u8) & 15) == 0);
@@ -720,6 +983,9 @@ k_fwd_tile_fx(const TileArgs a) {
             const int pl = k / SYN3R_TILE_W;
             fx_smem[pl * CELLS + FX_CELLS + (k - pl * SYN3R_TILE_W)] = (pl >= FX_ZKEY) ? ~0u : (pl == FX_WMAX ? 0x3f800000u : 0u);
         }
+#if SYN3R_FX_RESOLVE_STAGGER_NS
+        if ((warp >> 2) & 1) __nanosleep(SYN3R_FX_RESOLVE_STAGGER_NS);
+#endif
         for (int ly = warp; ly < SYN3R_TILE_H; ly += nwarps) {
 #else
         for (int ly = warp; ly <= SYN3R_TILE_H; ly += nwarps) {          // row TILE_H = the trash row (cleared only)
@@ -744,9 +1010,13 @@ k_fwd_tile_fx(const TileArgs a) {
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const unsigned off = n[j] * (unsigned)SYN3R_FX_MAGIC_BITS;     // every update added MAGIC_BITS + rint(.)
-                o[j] = fx_resolve_cell(wm[j], S[j] - off, (int)(i0[j] - off), (int)(i1[j] - off), (int)(i2[j] - off), wi[j],
-                                       a.flags, cscale, gate);
-                if (vec || lane * 4 + j < tw) bad = bad || o[j].bad;
+                if (gated)
+                    o[j] = fx_resolve_cell<true>(wm[j], S[j] - off, (int)(i0[j] - off), (int)(i1[j] - off), (int)(i2[j] - off),
+                                                 wi[j], cscale, gate);
+                else
+                    o[j] = fx_resolve_cell<false>(wm[j], S[j] - off, (int)(i0[j] - off), (int)(i1[j] - off), (int)(i2[j] - off),
+                                                  wi[j], cscale, gate);
+                range = max(range, (vec || lane * 4 + j < tw) ? o[j].range : 0u);
             }
             if (vec) {
                 st_once_u32(reinterpret_cast<unsigned *>(a.out_mask + q), (unsigned)o[0].m | ((unsigned)o[1].m << 8) |
@@ -801,10 +1071,22 @@ k_fwd_tile_fx(const TileArgs a) {
                 }
             }
         }
-        if (bad) ctl[7] = 1;
+        if ((a.flags & SYN3R_FWD_IS_IMAGE) && range > 0x43800000u) ctl[7] = 1;    // :121-125
         __syncthreads();
         if (tid == 0 && ctl[7] && a.out_status) atomicOr(a.out_status + slot, 1);
+#if SYN3R_FX_PHASE_CLOCKS
+        if (tid == 0) {                 // PAIR mode, FLAT cull only (ctl[10..13] are written there)
+            const unsigned t4 = (unsigned)clock(), cull = (unsigned)ctl[10] - ph_tb, t2 = (unsigned)ctl[11] - ph_tb;
+            const unsigned f1 = min((unsigned)ctl[12], t2), t3 = ph_t3 - ph_tb, f2 = max(min((unsigned)ctl[13], t3), t2);
+            ph[1] += cull; ph[2] += f1 - cull; ph[3] += t2 - f1; ph[4] += f2 - t2; ph[5] += t3 - f2; ph[6] += t4 - ph_t3;
+            ph[7] += 1;
+        }
+#endif
     }
+#if SYN3R_FX_PHASE_CLOCKS
+    if (tid == 0)
+        for (int k = 0; k < 8; ++k) g_fx_phase[(blockIdx.x & 1023) * 8 + k] = ph[k];
+#endif
 }
 
 }  // namespace syn3r

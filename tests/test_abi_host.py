@@ -41,8 +41,9 @@ def test_workspace_query_is_pure_host_arithmetic():
     leg = nat.FWD_LEGACY_GLOBAL
     assert L.syn3r_fwd_workspace_bytes(576, 1024, 3, 75, 75, leg) >= 75 * hw * 16
     assert L.syn3r_fwd_workspace_bytes(576, 1024, 3, 75, 75, leg | nat.FWD_WINNER) >= 75 * hw * 24
-    # tile path: no per-pixel accumulators in global memory, only block statistics and cell boxes
-    assert 0 < L.syn3r_fwd_workspace_bytes(576, 1024, 3, 75, 75, nat.FWD_WINNER) < 4 << 20
+    # tile path: no per-pixel accumulators in global memory, only block statistics, cell boxes and the per-(pair, tile)
+    # block lists (75 pairs x 96 tiles x 192 entries = 5.5 MB): 1 % of the 708 MB the global accumulators took
+    assert 0 < L.syn3r_fwd_workspace_bytes(576, 1024, 3, 75, 75, nat.FWD_WINNER) < 10 << 20
     assert L.syn3r_fwd_workspace_bytes(0, 1024, 3, 75, 75, 0) == 0
     assert L.syn3r_inv_workspace_bytes(75) % 256 == 0
 
