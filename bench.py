@@ -48,6 +48,8 @@ def parse_args():
     ap.add_argument("--no-post", action="store_true", help="skip the SURVEY 8f kernels' roofline object")
     ap.add_argument("--cpu-sample-seconds", type=float, default=12.0)
     ap.add_argument("--e2e-chunks", type=int, default=4, help="slot ranges whose D2H overlaps the next range's kernels")
+    ap.add_argument("--e2e-equal-ranges", action="store_true",
+                    help="equal slot ranges instead of the doubling ramp (A/B: the first D2H then starts later)")
     ap.add_argument("--gather", default="auto", choices=["auto", "nccl", "peer"],
                     help="N > 1: how finished frames reach rank 0 (auto: direct peer stores when symmetric memory works)")
     ap.add_argument("--gather-chunks", type=int, default=4, help="N > 1, nccl: slot ranges whose send overlaps the next range")
@@ -585,7 +587,7 @@ def e2e_single(args, wl, share, timed, mpix_step, big):
 
     def measure(plan, rgbd_h, tgt_h, how):
         def step_e2e():
-            plan.step_host(rgbd_h, tgt_h, chunks=args.e2e_chunks)
+            plan.step_host(rgbd_h, tgt_h, chunks=args.e2e_chunks, ramp=False if args.e2e_equal_ranges else None)
         for _ in range(2):
             step_e2e()
         ms_e = timed(step_e2e, max(3, args.steps // (4 if big else 1)))
@@ -600,6 +602,7 @@ def e2e_single(args, wl, share, timed, mpix_step, big):
     e2e_all = None
     packed = (wl.H * wl.W) % 16 == 0
     how = (f"TrajectoryWarp.step_host: pinned H2D of RGB-D (+ target depth) on an upload stream, kernels in {args.e2e_chunks} "
+           + ("equal " if args.e2e_equal_ranges else "doubling (equal for the post=True plan) ") +
            "slot ranges (uint8 frame + hole mask + winner" + (" + consistency masks" if wl.consistency else "") + "), D2H of "
            "the outputs the reference's forward_warp / inverse_warp return to their callers, overlapping the next range")
     if packed:

@@ -116,3 +116,15 @@ def test_product_fails_loudly_without_gpu():
     tr = synth.make_trajectory(1, 1, 8, 8, seed=4)
     with pytest.raises(nat.Syn3rNativeError):
         fw.forward_warp(tr.rgb[0], None, tr.depth[0], tr.pose_src[0], tr.pose_tgt[0], tr.K, None)
+
+
+def test_step_host_slot_ranges_cover_every_slot_once():
+    from syn3r_b200.trajectory import TrajectoryWarp
+    for n_slots in (1, 2, 3, 4, 5, 10, 25, 75, 100, 1000):
+        for chunks in (1, 2, 3, 4, 5, 8):
+            for ramp in (True, False):
+                b = TrajectoryWarp.slot_ranges(n_slots, chunks, ramp)
+                assert b[0] == 0 and b[-1] == n_slots and len(b) == min(chunks, n_slots) + 1
+                assert all(b[i] < b[i + 1] for i in range(len(b) - 1)), (n_slots, chunks, ramp, b)
+    # the ramp starts small: the first device-to-host copy of config B's 75 pair warps waits for 5 of them, not 18
+    assert TrajectoryWarp.slot_ranges(75, 4) == [0, 5, 15, 35, 75]
