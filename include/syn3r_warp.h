@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SYN3R_ABI_VERSION 14
+#define SYN3R_ABI_VERSION 15
 
 enum {
     SYN3R_OK = 0,
@@ -261,6 +261,19 @@ int syn3r_latent_top_masks(const float *pred, const float *cond_latents, const f
 size_t syn3r_mean_uncertainty_workspace_bytes(int P);
 int syn3r_mean_uncertainty_batched(const float *soft, int P, int H, int W, float *out_mean, void *workspace,
                                    size_t workspace_bytes, void *stream);
+
+/* syn3r_mean_uncertainty_batched without a workspace, for callers that cannot allocate device memory (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The chunk partials live in a file-scope device array inside the library
+ * (SYN3R_MEAN_UNCERTAINTY_STATIC_MAX_P x 64 doubles = 2 MiB on every GPU that loads the library, until exit); the call
+ * allocates nothing (no cudaMalloc / cudaFree, no allocating library routine).  P above the maximum returns
+ * SYN3R_EWORKSPACE with a message.  Same arguments, arithmetic and result bits as syn3r_mean_uncertainty_batched.
+ * All calls share the one array, which keeps the previous call's contents (nothing needs to start at zero: every
+ * partial that is read is written first); calls that OVERLAP on the GPU - different streams with no ordering between
+ * them, on the same device - race on it.  Calls on one stream, or ordered by events, are safe. */
+#define SYN3R_MEAN_UNCERTAINTY_STATIC_MAX_P 4096
+int syn3r_mean_uncertainty_static_max_p(void);
+int syn3r_mean_uncertainty_static(const float *soft, int P, int H, int W, float *out_mean, void *stream);
 
 #ifdef __cplusplus
 }

@@ -4,6 +4,8 @@
 #include "flow.cuh"
 #include "latent.cuh"
 
+#include <mutex>
+
 using namespace syn3r;
 
 extern "C" {
@@ -160,6 +162,62 @@ int syn3r_mean_uncertainty_batched(const float *soft, int P, int H, int W, float
     k_mean_uncertainty_partial<<<dim3(SYN3R_SC_BLOCKS, P), SYN3R_SC_THREADS, 0, st>>>(soft, hw, (double *)workspace);
     k_mean_uncertainty_final<<<(P + 127) / 128, 128, 0, st>>>((const double *)workspace, P, hw, out_mean);
     return check_cuda(cudaGetLastError(), "k_mean_uncertainty");
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// syn3r_mean_uncertainty_static: syn3r_mean_uncertainty_batched for callers that cannot allocate (CUDA graph capture,
+// serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The chunk partials live in a file-scope device array instead of a caller-owned workspace: 2 MiB per GPU
+// that loads the library, held until exit.  Every call shares it and it keeps the last call's contents: nothing has to
+// start at zero (the first kernel overwrites every partial the second one reads), but two calls that overlap on the
+// GPU (different streams, no ordering between them) race on it.
+// ---------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_mean_unc_scratch[(size_t)SYN3R_MEAN_UNCERTAINTY_STATIC_MAX_P * SYN3R_SC_BLOCKS];
+
+// In host code `g_mean_unc_scratch` is a host-side stand-in, not a device address: the address a kernel may use comes
+// from cudaGetSymbolAddress, once per device, with that device current.
+static int mean_unc_scratch_ptr(double **out) {
+    enum { MAX_DEV = 64 };
+    static std::mutex mu;
+    static double *ptrs[MAX_DEV] = {};
+    int dev = -1;
+    SYN3R_TRY_CUDA(cudaGetDevice(&dev));
+    SYN3R_REQUIRE(dev >= 0 && dev < MAX_DEV, "device ordinal out of range");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        double *p = nullptr;
+        SYN3R_TRY_CUDA(cudaGetSymbolAddress((void **)&p, g_mean_unc_scratch));
+        SYN3R_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return SYN3R_OK;
+}
+
+int syn3r_mean_uncertainty_static_max_p(void) { return SYN3R_MEAN_UNCERTAINTY_STATIC_MAX_P; }
+
+int syn3r_mean_uncertainty_static(const float *soft, int P, int H, int W, float *out_mean, void *stream) {
+    if (P == 0) return SYN3R_OK;
+    SYN3R_REQUIRE(soft && out_mean, "null required pointer");
+    SYN3R_REQUIRE(P > 0 && H > 0 && W > 0, "bad sizes");
+    if (P > SYN3R_MEAN_UNCERTAINTY_STATIC_MAX_P) {
+        set_error("syn3r_mean_uncertainty_static: P = %d exceeds the static scratch (at most %d frames per call); split the "
+                  "batch or use syn3r_mean_uncertainty_batched with a caller-owned workspace", P,
+                  SYN3R_MEAN_UNCERTAINTY_STATIC_MAX_P);
+        return SYN3R_EWORKSPACE;
+    }
+    SYN3R_REQUIRE(((size_t)H * W) % 4 == 0 || P == 1, "H*W must be a multiple of 4 for P > 1 (16-byte frame alignment)");
+    SYN3R_REQUIRE(((uintptr_t)soft & 15) == 0, "soft must be 16-byte aligned");
+    int rc = check_device();
+    if (rc != SYN3R_OK) return rc;
+    double *scratch = nullptr;
+    rc = mean_unc_scratch_ptr(&scratch);
+    if (rc != SYN3R_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t hw = (size_t)H * W;
+    k_mean_uncertainty_partial<<<dim3(SYN3R_SC_BLOCKS, P), SYN3R_SC_THREADS, 0, st>>>(soft, hw, scratch);
+    k_mean_uncertainty_final<<<(P + 127) / 128, 128, 0, st>>>(scratch, P, hw, out_mean);
+    return check_cuda(cudaGetLastError(), "k_mean_uncertainty (static scratch)");
 }
 
 }  // extern "C"
