@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SYN3R_ABI_VERSION 15
+#define SYN3R_ABI_VERSION 16
 
 enum {
     SYN3R_OK = 0,
@@ -261,6 +261,13 @@ int syn3r_latent_top_masks(const float *pred, const float *cond_latents, const f
 size_t syn3r_mean_uncertainty_workspace_bytes(int P);
 int syn3r_mean_uncertainty_batched(const float *soft, int P, int H, int W, float *out_mean, void *workspace,
                                    size_t workspace_bytes, void *stream);
+
+/* A/B switch of the lean consistency kernel (the syn3r_inverse_warp_batched call that asks only for mask_reproj /
+ * soft_mask_reproj / mask_warp): 1 (default) = k_reproj_masks2, two rows per thread in packed fp32 instructions;
+ * 0 = k_reproj_masks, one row per thread.  Both produce the same bits (tests/test_gpu_parity.py::
+ * test_packed_reproj_matches_scalar); the switch exists for that test and for timing.  Process-wide; returns the
+ * previous setting.  No reference counterpart. */
+int syn3r_set_reproj_packed(int on);
 
 /* syn3r_mean_uncertainty_batched without a workspace, for callers that cannot allocate device memory (code under CUDA
  * graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference: added at the

@@ -2,7 +2,7 @@
 #include <math.h>
 #include <string.h>
 
-#include "inverse_kernels.cuh"
+#include "inverse_packed.cuh"
 
 using namespace syn3r;
 
@@ -68,7 +68,15 @@ float reproj_threshold_sq(float bw) {
 
 }  // namespace
 
+static int g_reproj_packed = 1;
+
 extern "C" {
+
+int syn3r_set_reproj_packed(int on) {
+    const int was = g_reproj_packed;
+    g_reproj_packed = on ? 1 : 0;
+    return was;
+}
 
 size_t syn3r_inv_workspace_bytes(int n_pairs) {
     if (n_pairs <= 0) return 0;
@@ -113,6 +121,19 @@ int syn3r_inverse_warp_batched(const float *src_img, const float *src_depth, int
         SYN3R_REQUIRE(P <= 65535, "lean path: at most 65535 pairs per call");
         dim3 gl((W + SYN3R_RM_COLS - 1) / SYN3R_RM_COLS, (H + SYN3R_RM_ROWS - 1) / SYN3R_RM_ROWS, P);
         const float bw_sq = reproj_threshold_sq(bandwidth), inv_bw = 1.0f / bandwidth;
+        if (g_reproj_packed && !out->reproj_err && cam.rc_wm1 != 0.0f && cam.rc_hm1 != 0.0f) {
+            gl.y = (H + SYN3R_RM2_ROWS - 1) / SYN3R_RM2_ROWS;
+            SYN3R_REQUIRE(gl.y <= 65535, "lean path: H too large");
+            // two rows per thread in packed fp32 instructions (inverse_packed.cuh): the same bits, half the issue slots
+            const PkConst pkc{-0.0f, 1.0f, -1.0f};
+            if (src_depth_stride == 4)
+                k_reproj_masks2<4><<<gl, SYN3R_RM_COLS, 0, st>>>(cam, pr, src_depth, tgt_depth, H, W, bw_sq, inv_bw, pkc,
+                                                               out->mask_reproj, out->soft_mask_reproj, out->mask_warp);
+            else
+                k_reproj_masks2<1><<<gl, SYN3R_RM_COLS, 0, st>>>(cam, pr, src_depth, tgt_depth, H, W, bw_sq, inv_bw, pkc,
+                                                               out->mask_reproj, out->soft_mask_reproj, out->mask_warp);
+            return check_cuda(cudaGetLastError(), "k_reproj_masks2");
+        }
 #define SYN3R_RM_LAUNCH(DS, ERR)                                                                                     \
     k_reproj_masks<DS, ERR><<<gl, SYN3R_RM_COLS, 0, st>>>(cam, pr, src_depth, tgt_depth, H, W, bandwidth, bw_sq, inv_bw, \
                                                           out->mask_reproj, out->soft_mask_reproj, out->reproj_err,   \

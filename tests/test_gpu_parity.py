@@ -399,3 +399,65 @@ def test_step_host_matches_run():
     for k, v in got.items():
         if k.startswith("out_"):
             assert torch.equal(torch.nan_to_num(v.float()), torch.nan_to_num(ref[k].float())), k
+
+
+@pytest.mark.parametrize("case", ["generic", "hostile", "identity", "projective", "tiny_scene"])
+@pytest.mark.parametrize("shape", [(61, 97), (64, 256), (1, 40)])
+def test_packed_reproj_matches_scalar(case, shape):
+    """k_reproj_masks2 (two rows per thread, packed fp32 instructions, range-tested division fast path with the scalar
+    arithmetic as its slow path) against k_reproj_masks (one row per thread, IEEE divisions): the same BITS on every
+    output, for both depth layouts, with odd heights, depths that are zero / negative / NaN / inf / denormal / huge, an
+    identity pose (exact zeros everywhere), a pose matrix with a projective bottom row and a scene of size 1e-15."""
+    from syn3r_b200 import _native as nat, warp as w
+    H, W = shape
+    S, T = 2, 3
+    tr = synth.make_trajectory(S, T, H, W, seed=71 + H, pose_step=2.0)
+    depth, depth_tgt = tr.depth.copy(), tr.depth_tgt.copy()
+    pose_src, pose_tgt = tr.pose_src.copy(), tr.pose_tgt.copy()
+    rng = np.random.default_rng(5)
+    if case == "hostile":
+        for d in (depth, depth_tgt):
+            flat = d.reshape(-1)
+            idx = rng.choice(flat.size, size=max(8, flat.size // 6), replace=False)
+            flat[idx] = rng.choice(np.array([0.0, -0.0, -1.5, np.nan, np.inf, -np.inf, 1e-42, 1e-30, 1e30, 3e38, 1e-12],
+                                            np.float32), size=idx.size)
+    elif case == "identity":
+        pose_tgt[0] = pose_src[0]
+        depth_tgt[0] = depth[0]
+    elif case == "tiny_scene":
+        depth *= 1e-15
+        depth_tgt *= 1e-15
+        pose_src[:, :3, 3] *= 1e-15
+        pose_tgt[:, :3, 3] *= 1e-15
+    ps, pt = synth.all_pairs(S, T)
+    par = w.inverse_pair_params(pose_src, pose_tgt, ps, pt)
+    if case == "projective":
+        par = par.copy()
+        par[:, :, 12:16] += np.array([1e-4, -2e-4, 3e-4, 0.01], np.float32)     # w != 1: the scalar path decides
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    want = ("mask_reproj", "soft_mask_reproj", "mask_warp")
+    rgbd = up(w.pack_rgbd(tr.rgb, depth))
+    L = nat.lib()
+    res = {}
+    for packed in (1, 0):
+        was = L.syn3r_set_reproj_packed(packed)
+        try:
+            planar = w.inverse_warp_batched(None, up(depth), up(depth_tgt), tr.K.astype(np.float32), up(par), up(ps), up(pt),
+                                            bandwidth=3.0, want=want)
+            lane = w.inverse_warp_batched(None, None, up(depth_tgt), tr.K.astype(np.float32), up(par), up(ps), up(pt), rgbd=rgbd,
+                                          bandwidth=3.0, want=want)
+            torch.cuda.synchronize()
+        finally:
+            L.syn3r_set_reproj_packed(was)
+        res[packed] = (planar, lane)
+    for k in want:
+        for layout in (0, 1):
+            a, b = res[1][layout][k].cpu().numpy(), res[0][layout][k].cpu().numpy()
+            if a.dtype == np.float32:
+                assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), (case, shape, k, layout)
+            else:
+                assert np.array_equal(a, b), (case, shape, k, layout)
+        a, b = res[1][0][k].cpu().numpy(), res[1][1][k].cpu().numpy()                      # planar == RGB-D lane
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32)) if a.dtype == np.float32 else np.array_equal(a, b)
+    if case == "generic":
+        assert 0 < int(res[1][0]["mask_reproj"].sum()) < res[1][0]["mask_reproj"].numel() or H == 1
