@@ -445,7 +445,7 @@ def run_ours(args):
             def step():
                 tw.run()
                 peer.barrier()
-            gather_info = {"how": "direct peer stores: the resolve step of k_fwd_tile_fx and k_reproj_masks write into rank 0's "
+            gather_info = {"how": "direct peer stores: the resolve step of k_fwd_tile_fx and k_reproj_masks2 write into rank 0's "
                                   "symmetric buffers over NVLink (no send/recv, no staging copy); one barrier closes the step"}
             nbytes = peer.bytes_received(wire)
         else:

@@ -321,7 +321,7 @@ class TrajectoryWarp:
 
     def launches_per_run(self) -> int:
         """Kernels of libsyn3r_warp.so per run() (memsets not counted): k_src_stats, k_fwd_prep (bounds), k_fwd_prep (pruned max z'),
-        k_fwd_finalize, k_fwd_tile_fx, k_fwd_tile (redo list, normally empty) (+ k_reproj_masks)."""
+        k_fwd_finalize, k_fwd_tile_fx, k_fwd_tile (redo list, normally empty) (+ k_reproj_masks2)."""
         return (6 + (1 if self.consistency else 0) + ((2 if self.consistency else 1) if self.post else 0) +
                 ((2 if self.consistency else 1) if self.pack_masks else 0))
 
