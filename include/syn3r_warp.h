@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SYN3R_ABI_VERSION 16
+#define SYN3R_ABI_VERSION 17
 
 enum {
     SYN3R_OK = 0,
@@ -268,6 +268,14 @@ int syn3r_mean_uncertainty_batched(const float *soft, int P, int H, int W, float
  * test_packed_reproj_matches_scalar); the switch exists for that test and for timing.  Process-wide; returns the
  * previous setting.  No reference counterpart. */
 int syn3r_set_reproj_packed(int on);
+
+/* A/B switch of the forward tile kernel in PAIR mode with per-(pair, tile) block lists: 1 = k_fwd_tile_fx_ov, whose
+ * resolve step is split so that its second phase overlaps the next work item's first sweep (three barriers per item
+ * instead of five); 0 (default) = k_fwd_tile_fx.  Measured equal (1.191 vs 1.192 ms on config B), so the simpler kernel
+ * stays the default.  Same bits either way
+ * (tests/test_gpu_parity.py::test_overlapped_tile_kernel_matches); for that test and for timing.  Process-wide; returns
+ * the previous setting.  No reference counterpart. */
+int syn3r_set_fx_overlap(int on);
 
 /* syn3r_mean_uncertainty_batched without a workspace, for callers that cannot allocate device memory (code under CUDA
  * graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference: added at the

@@ -22,7 +22,7 @@ FWD_LEGACY_GLOBAL = 1 << 4
 FWD_FP32_TILE = 1 << 5
 FWD_PHASE_ZMAX, FWD_PHASE_SPLAT, FWD_PHASE_RESOLVE = 1 << 8, 1 << 9, 1 << 10
 
-ABI_VERSION = 16
+ABI_VERSION = 17
 
 c_void_p, c_int, c_size_t, c_float = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t, ctypes.c_float
 
@@ -66,6 +66,7 @@ SIGNATURES = {
     "syn3r_mean_uncertainty_workspace_bytes": (c_size_t, [c_int]),
     "syn3r_mean_uncertainty_batched": (c_int, [c_void_p] + [c_int] * 3 + [c_void_p] * 2 + [c_size_t, c_void_p]),
     "syn3r_set_reproj_packed": (c_int, [c_int]),
+    "syn3r_set_fx_overlap": (c_int, [c_int]),
     "syn3r_mean_uncertainty_static_max_p": (c_int, []),
     "syn3r_mean_uncertainty_static": (c_int, [c_void_p] + [c_int] * 3 + [c_void_p] * 2),
 }

@@ -2,7 +2,7 @@
 #include <stdarg.h>
 #include <string.h>
 
-#include "forward_fx.cuh"
+#include "forward_fx_overlap.cuh"
 
 namespace syn3r {
 
@@ -175,9 +175,38 @@ static int launch_tile_fx_as(const TileArgs &ta, int n_items, cudaStream_t st) {
     return SYN3R_OK;
 }
 // frames of up to SYN3R_FX_FLAT source blocks (1024 x 576 and smaller) take the one-pass cull
+#if SYN3R_FX_OV_AVAILABLE
+// PAIR mode with block lists: the kernel that overlaps an item's resolve step with the next item's sweep 1
+template <bool WINNER>
+static int launch_tile_fx_ov(const TileArgs &ta, int n_items, cudaStream_t st) {
+    static thread_local int configured_dev = -1;
+    const size_t smem = fx_ov_smem_bytes(WINNER), smem_redo = tile_smem_bytes(WINNER);
+    int dev = -1;
+    SYN3R_TRY_CUDA(cudaGetDevice(&dev));
+    if (configured_dev != dev) {
+        SYN3R_TRY_CUDA(cudaFuncSetAttribute(k_fwd_tile_fx_ov<WINNER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SYN3R_TRY_CUDA(cudaFuncSetAttribute(k_fwd_tile<WINNER, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)smem_redo));
+        configured_dev = dev;
+    }
+    int grid = sm_count();
+    if (grid > n_items) grid = n_items;
+    k_fwd_tile_fx_ov<WINNER><<<grid, SYN3R_TILE_THREADS, smem, st>>>(ta);
+    TileArgs tr = ta;
+    tr.redo_mode = 1;
+    k_fwd_tile<WINNER, false><<<grid, SYN3R_TILE_THREADS, smem_redo, st>>>(tr);
+    return SYN3R_OK;
+}
+#endif
+
+static int g_fx_overlap = 0;       // syn3r_set_fx_overlap (A/B switch; off: measured equal to k_fwd_tile_fx, see forward_fx_overlap.cuh)
+
 template <bool WINNER>
 static int launch_tile_fx(const TileArgs &ta, int n_items, cudaStream_t st) {
     if (ta.g.nsb * SYN3R_SB_BLOCKS > SYN3R_FX_FLAT) return launch_tile_fx_as<WINNER, false, false>(ta, n_items, st);
+#if SYN3R_FX_OV_AVAILABLE
+    if (g_fx_overlap && !ta.pair_slot && ta.tile_cnt) return launch_tile_fx_ov<WINNER>(ta, n_items, st);
+#endif
     // PAIR mode with block lists: every work item is claimed and staged one item ahead
     if (SYN3R_FX_PREFETCH && !ta.pair_slot && ta.tile_cnt) return launch_tile_fx_as<WINNER, true, true>(ta, n_items, st);
     return launch_tile_fx_as<WINNER, true, false>(ta, n_items, st);
@@ -237,6 +266,12 @@ int syn3r_selftest_ddiv2(unsigned long long n, unsigned long long seed, int mode
 
 
 int syn3r_version(void) { return SYN3R_ABI_VERSION; }
+
+int syn3r_set_fx_overlap(int on) {
+    const int was = g_fx_overlap;
+    g_fx_overlap = on ? 1 : 0;
+    return was;
+}
 const char *syn3r_last_error(void) { return g_err; }
 
 int syn3r_device_info(int *sm, int *smem, int *major, int *minor) {

@@ -461,3 +461,34 @@ def test_packed_reproj_matches_scalar(case, shape):
         assert np.array_equal(a.view(np.uint32), b.view(np.uint32)) if a.dtype == np.float32 else np.array_equal(a, b)
     if case == "generic":
         assert 0 < int(res[1][0]["mask_reproj"].sum()) < res[1][0]["mask_reproj"].numel() or H == 1
+
+
+@pytest.mark.parametrize("shape", [(3, 5, 96, 160), (2, 3, 61, 97), (2, 2, 200, 300), (3, 4, 576, 1024)])
+def test_overlapped_tile_kernel_matches(shape):
+    """k_fwd_tile_fx_ov (resolve step split, its second phase overlapped with the next work item's first sweep, three
+    barriers per item) against k_fwd_tile_fx: the same BITS on every forward output, with and without the winner index,
+    for frames with ragged tiles (non-vector stores), several items per CTA and more items than CTAs."""
+    from syn3r_b200 import _native as nat, trajectory, warp as w
+    S, T, H, W = shape
+    tr = synth.make_trajectory(S, T, H, W, seed=90 + H, pose_step=2.0)
+    L = nat.lib()
+    res = {}
+    for winner in (True, False):
+        for ov in (1, 0):
+            was = L.syn3r_set_fx_overlap(ov)
+            try:
+                tw = trajectory.from_synth(tr, want_f32=True, want_u8=True, want_winner=winner, consistency=False)
+                tw.upload(torch.from_numpy(w.pack_rgbd(tr.rgb, tr.depth)))
+                o = tw.run()
+                o2 = tw.run()                      # a second run on the same workspace: nothing stale in the planes
+                torch.cuda.synchronize()
+            finally:
+                L.syn3r_set_fx_overlap(was)
+            assert int(o.status.max().item()) == 0
+            res[(winner, ov)] = {k: getattr(o2, k).cpu().numpy().copy() for k in ("rgb_f32", "rgb_u8", "mask") +
+                                 (("winner",) if winner else ())}
+        for k, a in res[(winner, 1)].items():
+            b = res[(winner, 0)][k]
+            same = np.array_equal(a.view(np.uint32), b.view(np.uint32)) if a.dtype == np.float32 else np.array_equal(a, b)
+            assert same, (shape, winner, k, int((a != b).sum()))
+    assert res[(True, 1)]["mask"].any()
