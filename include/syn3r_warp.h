@@ -107,7 +107,9 @@ int syn3r_device_info(int *sm_count, int *smem_optin_bytes, int *cc_major, int *
  *                                     index; -1 = hole
  *   out_flow    [P,H,W,2]  f64  nullable: flow12 (:177)
  *   out_status  [n_slots]  i32  nullable: bit0 = colour-range assert of :121-125 failed
- *   workspace   >= syn3r_fwd_workspace_bytes(...) bytes, 256-byte aligned
+ *   workspace   >= syn3r_fwd_workspace_bytes(...) bytes, 256-byte aligned: block statistics, per-(pair, block) cell
+ *               boxes and, for frames of up to 2304 source blocks (1024 x 576), per-(pair, target tile) block lists
+ *               (768 B per pair and 128 x 48 tile: 5.5 MB for 75 pairs at 576 x 1024); no per-pixel accumulators
  * ------------------------------------------------------------------------------------------- */
 size_t syn3r_fwd_workspace_bytes(int H, int W, int S, int n_pairs, int n_slots, int flags);
 
